@@ -1,0 +1,475 @@
+// oracle/ref_shim.cpp — TEST INFRASTRUCTURE ONLY.
+//
+// A flat C ABI over the *unmodified* reference library (oracle/_ref/libfheref.so, compiled by
+// oracle/Makefile from the sources under /root/reference).  Nothing here is shipped or linked into
+// libluxb200.so; only tests/, __graft_entry__.smoke() and bench.py's reference / cpu_baseline legs
+// load it.  Every function drives the reference through its own public API:
+//   BinFHEContext            src/binfhe/include/binfhecontext.h:130-447
+//   BinFHEScheme / EvalAcc   src/binfhe/include/binfhe-base-scheme.h, rgsw-acc.h:60-99
+//   LWEEncryptionScheme      src/binfhe/include/lwe-pke.h
+//   ChineseRemainderTransformFTT / NativePoly   src/core/include/math/hal/intnat/transformnat.h
+//   ILDCRTParams             src/core/include/lattice/ildcrtparams.h:100-118
+#include "binfhecontext.h"
+#include "lattice/lat-hal.h"
+#include "math/math-hal.h"
+#include "math/nbtheory.h"
+
+#include <omp.h>
+#include <chrono>
+#include <cstdint>
+#include <cstring>
+#include <memory>
+#include <vector>
+
+using namespace lux::fhe;
+
+struct RefCtx {
+    BinFHEContext cc;
+    LWEPrivateKey sk;
+    bool haveKeys = false;
+};
+
+static LWECiphertext make_ct(const uint64_t* a, uint64_t b, uint32_t n, uint64_t mod, uint64_t p = 4) {
+    NativeVector v(n, NativeInteger(mod));
+    for (uint32_t i = 0; i < n; ++i)
+        v[i] = NativeInteger(a[i]);
+    auto ct = std::make_shared<LWECiphertextImpl>(std::move(v), NativeInteger(b));
+    ct->SetptModulus(p);
+    return ct;
+}
+
+static void put_ct(ConstLWECiphertext& ct, uint64_t* a, uint64_t* b) {
+    uint32_t n = ct->GetLength();
+    for (uint32_t i = 0; i < n; ++i)
+        a[i] = ct->GetA(i).ConvertToInt();
+    *b = ct->GetB().ConvertToInt();
+}
+
+extern "C" {
+
+void* ref_ctx_create(int paramset, int method) {
+    try {
+        auto* h = new RefCtx();
+        h->cc.GenerateBinFHEContext(static_cast<BINFHE_PARAMSET>(paramset), static_cast<BINFHE_METHOD>(method));
+        return h;
+    }
+    catch (...) {
+        return nullptr;
+    }
+}
+
+void ref_ctx_destroy(void* hv) {
+    delete static_cast<RefCtx*>(hv);
+}
+
+// out[0..15]: n N q Q qKS baseKS baseG baseR digitsG numAutoKeys keyDist psi(2N-th root) digitsKS method
+int ref_ctx_params(void* hv, uint64_t* out) {
+    auto* h   = static_cast<RefCtx*>(hv);
+    auto lwe  = h->cc.GetParams()->GetLWEParams();
+    auto rgsw = h->cc.GetParams()->GetRingGSWParams();
+    out[0]    = lwe->Getn();
+    out[1]    = lwe->GetN();
+    out[2]    = lwe->Getq().ConvertToInt();
+    out[3]    = lwe->GetQ().ConvertToInt();
+    out[4]    = lwe->GetqKS().ConvertToInt();
+    out[5]    = lwe->GetBaseKS();
+    out[6]    = rgsw->GetBaseG();
+    out[7]    = rgsw->GetBaseR();
+    out[8]    = rgsw->GetDigitsG();
+    out[9]    = rgsw->GetNumAutoKeys();
+    out[10]   = static_cast<uint64_t>(lwe->GetKeyDist());
+    out[11]   = rgsw->GetPolyParams()->GetRootOfUnity().ConvertToInt();
+    out[12]   = static_cast<uint64_t>(
+        std::ceil(log(lwe->GetqKS().ConvertToDouble()) / log(static_cast<double>(lwe->GetBaseKS()))));
+    out[13] = static_cast<uint64_t>(rgsw->GetMethod());
+    return 0;
+}
+
+int ref_keygen(void* hv) {
+    auto* h = static_cast<RefCtx*>(hv);
+    try {
+        h->sk = h->cc.KeyGen();
+        h->cc.BTKeyGen(h->sk);
+        h->haveKeys = true;
+        return 0;
+    }
+    catch (...) {
+        return -1;
+    }
+}
+
+// secret key as signed values in (-mod/2, mod/2]
+int ref_get_sk(void* hv, int64_t* out) {
+    auto* h        = static_cast<RefCtx*>(hv);
+    const auto& sv = h->sk->GetElement();
+    uint64_t mod   = sv.GetModulus().ConvertToInt();
+    for (uint32_t i = 0; i < sv.GetLength(); ++i) {
+        uint64_t v = sv[i].ConvertToInt();
+        out[i]     = v > mod / 2 ? static_cast<int64_t>(v) - static_cast<int64_t>(mod) : static_cast<int64_t>(v);
+    }
+    return 0;
+}
+
+// BSK dims: d0 d1 d2 of RingGSWACCKeyImpl, then rows (of entry [0][0][0]) and N
+int ref_bsk_dims(void* hv, uint64_t* out) {
+    auto* h        = static_cast<RefCtx*>(hv);
+    const auto& ek = h->cc.GetRefreshKey()->GetElements();
+    out[0]         = ek.size();
+    out[1]         = ek[0].size();
+    out[2]         = ek[0][0].size();
+    out[3]         = 0;
+    out[4]         = 0;
+    for (auto& x : ek)
+        for (auto& y : x)
+            for (auto& z : y)
+                if (z) {
+                    out[3] = z->GetElements().size();
+                    out[4] = z->GetElements()[0][0].GetLength();
+                    return 0;
+                }
+    return 0;
+}
+
+// Dump entry [i0][i1][i2] (rows x 2 x N, EVALUATION format, reference order) ; returns rows, 0 if null
+int ref_bsk_entry(void* hv, uint32_t i0, uint32_t i1, uint32_t i2, uint64_t* out) {
+    auto* h        = static_cast<RefCtx*>(hv);
+    const auto& ek = h->cc.GetRefreshKey()->GetElements();
+    const auto& e  = ek[i0][i1][i2];
+    if (!e)
+        return 0;
+    const auto& el = e->GetElements();
+    size_t pos     = 0;
+    for (auto& row : el)
+        for (auto& poly : row) {
+            uint32_t N = poly.GetLength();
+            for (uint32_t k = 0; k < N; ++k)
+                out[pos++] = poly[k].ConvertToInt();
+        }
+    return static_cast<int>(el.size());
+}
+
+// KSK: A [N][baseKS][digits][n], B [N][baseKS][digits]
+int ref_ksk_dump(void* hv, uint64_t* A, uint64_t* B) {
+    auto* h        = static_cast<RefCtx*>(hv);
+    const auto& kA = h->cc.GetSwitchKey()->GetElementsA();
+    const auto& kB = h->cc.GetSwitchKey()->GetElementsB();
+    size_t pa = 0, pb = 0;
+    for (size_t i = 0; i < kA.size(); ++i)
+        for (size_t j = 0; j < kA[i].size(); ++j)
+            for (size_t k = 0; k < kA[i][j].size(); ++k) {
+                const auto& v = kA[i][j][k];
+                for (uint32_t t = 0; t < v.GetLength(); ++t)
+                    A[pa++] = v[t].ConvertToInt();
+                B[pb++] = kB[i][j][k].ConvertToInt();
+            }
+    return 0;
+}
+
+int ref_encrypt(void* hv, int64_t m, uint64_t p, uint64_t mod, uint64_t* a, uint64_t* b) {
+    auto* h = static_cast<RefCtx*>(hv);
+    auto ct = h->cc.Encrypt(h->sk, m, SMALL_DIM, p, NativeInteger(mod));
+    put_ct(ct, a, b);
+    return 0;
+}
+
+int64_t ref_decrypt(void* hv, const uint64_t* a, uint64_t b, uint32_t len, uint64_t mod, uint64_t p) {
+    auto* h = static_cast<RefCtx*>(hv);
+    auto ct = make_ct(a, b, len, mod, p);
+    LWEPlaintext r;
+    h->cc.Decrypt(h->sk, ct, &r, p);
+    return r;
+}
+
+// count independent 2-input gates; inputs [count][n] / [count]; out_len = n (or N if extended)
+int ref_evalbingate(void* hv, int gate, const uint64_t* a1, const uint64_t* b1, const uint64_t* a2,
+                    const uint64_t* b2, uint64_t* oa, uint64_t* ob, uint64_t count, int extended, int threads) {
+    auto* h      = static_cast<RefCtx*>(hv);
+    auto lwe     = h->cc.GetParams()->GetLWEParams();
+    uint32_t n   = lwe->Getn();
+    uint64_t q   = lwe->Getq().ConvertToInt();
+    uint32_t on  = extended ? lwe->GetN() : n;
+    int failures = 0;
+#pragma omp parallel for num_threads(threads > 0 ? threads : 1) schedule(dynamic)
+    for (uint64_t i = 0; i < count; ++i) {
+        try {
+            auto c1 = make_ct(a1 + i * n, b1[i], n, q);
+            auto c2 = make_ct(a2 + i * n, b2[i], n, q);
+            auto r  = h->cc.EvalBinGate(static_cast<BINGATE>(gate), c1, c2, extended != 0);
+            put_ct(r, oa + i * on, ob + i);
+        }
+        catch (...) {
+#pragma omp atomic
+            failures++;
+        }
+    }
+    return failures;
+}
+
+// multi-input gates (AND3/OR3/MAJORITY/AND4/OR4/CMUX): inputs [count][k][n]
+int ref_evalbingate_multi(void* hv, int gate, uint32_t k, const uint64_t* a, const uint64_t* b, uint64_t* oa,
+                          uint64_t* ob, uint64_t count, uint64_t p, int threads) {
+    auto* h      = static_cast<RefCtx*>(hv);
+    auto lwe     = h->cc.GetParams()->GetLWEParams();
+    uint32_t n   = lwe->Getn();
+    uint64_t q   = lwe->Getq().ConvertToInt();
+    int failures = 0;
+#pragma omp parallel for num_threads(threads > 0 ? threads : 1) schedule(dynamic)
+    for (uint64_t i = 0; i < count; ++i) {
+        try {
+            std::vector<LWECiphertext> v;
+            for (uint32_t j = 0; j < k; ++j)
+                v.push_back(make_ct(a + (i * k + j) * n, b[i * k + j], n, q, p));
+            auto r = h->cc.EvalBinGate(static_cast<BINGATE>(gate), v);
+            put_ct(r, oa + i * n, ob + i);
+        }
+        catch (...) {
+#pragma omp atomic
+            failures++;
+        }
+    }
+    return failures;
+}
+
+int ref_bootstrap(void* hv, const uint64_t* a, const uint64_t* b, uint64_t* oa, uint64_t* ob, uint64_t count,
+                  uint64_t p, int extended, int threads) {
+    auto* h     = static_cast<RefCtx*>(hv);
+    auto lwe    = h->cc.GetParams()->GetLWEParams();
+    uint32_t n  = lwe->Getn();
+    uint64_t q  = lwe->Getq().ConvertToInt();
+    uint32_t on = extended ? lwe->GetN() : n;
+#pragma omp parallel for num_threads(threads > 0 ? threads : 1) schedule(dynamic)
+    for (uint64_t i = 0; i < count; ++i) {
+        auto c = make_ct(a + i * n, b[i], n, q, p);
+        auto r = h->cc.Bootstrap(c, extended != 0);
+        put_ct(r, oa + i * on, ob + i);
+    }
+    return 0;
+}
+
+// EvalFunc with an explicit LUT of length q (ciphertext modulus). Returns -1 if the reference throws.
+int ref_evalfunc(void* hv, const uint64_t* a, const uint64_t* b, const uint64_t* lut, uint64_t lutlen, uint64_t* oa,
+                 uint64_t* ob, uint64_t count, uint64_t ctmod, int threads) {
+    auto* h    = static_cast<RefCtx*>(hv);
+    auto lwe   = h->cc.GetParams()->GetLWEParams();
+    uint32_t n = lwe->Getn();
+    std::vector<NativeInteger> L(lutlen);
+    for (uint64_t i = 0; i < lutlen; ++i)
+        L[i] = NativeInteger(lut[i]);
+    int failures = 0;
+#pragma omp parallel for num_threads(threads > 0 ? threads : 1) schedule(dynamic)
+    for (uint64_t i = 0; i < count; ++i) {
+        try {
+            auto c = make_ct(a + i * n, b[i], n, ctmod);
+            auto r = h->cc.EvalFunc(c, L);
+            put_ct(r, oa + i * n, ob + i);
+        }
+        catch (...) {
+#pragma omp atomic
+            failures++;
+        }
+    }
+    return failures ? -1 : 0;
+}
+
+uint64_t ref_get_beta(void* hv) {
+    return static_cast<RefCtx*>(hv)->cc.GetBeta().ConvertToInt();
+}
+
+// Blind rotation only (RingGSWAccumulator::EvalAcc through the scheme bound in the context):
+// acc [2][N] in EVALUATION format in/out; a [n] mod amod.
+int ref_evalacc(void* hv, const uint64_t* a, uint64_t amod, uint64_t* acc) {
+    auto* h     = static_cast<RefCtx*>(hv);
+    auto params = h->cc.GetParams();
+    auto rgsw   = params->GetRingGSWParams();
+    auto pp     = rgsw->GetPolyParams();
+    uint32_t N  = rgsw->GetN();
+    uint32_t n  = params->GetLWEParams()->Getn();
+    std::vector<NativePoly> res(2);
+    for (int c = 0; c < 2; ++c) {
+        res[c] = NativePoly(pp, Format::EVALUATION, true);
+        for (uint32_t k = 0; k < N; ++k)
+            res[c][k] = NativeInteger(acc[c * N + k]);
+    }
+    auto accct = std::make_shared<RLWECiphertextImpl>(std::move(res));
+    NativeVector av(n, NativeInteger(amod));
+    for (uint32_t i = 0; i < n; ++i)
+        av[i] = NativeInteger(a[i]);
+    std::shared_ptr<RingGSWAccumulator> sch;
+    switch (rgsw->GetMethod()) {
+        case AP:
+            sch = std::make_shared<RingGSWAccumulatorDM>();
+            break;
+        case GINX:
+            sch = std::make_shared<RingGSWAccumulatorCGGI>();
+            break;
+        default:
+            sch = std::make_shared<RingGSWAccumulatorLMKCDEY>();
+    }
+    sch->EvalAcc(rgsw, h->cc.GetRefreshKey(), accct, av);
+    for (int c = 0; c < 2; ++c)
+        for (uint32_t k = 0; k < N; ++k)
+            acc[c * N + k] = accct->GetElements()[c][k].ConvertToInt();
+    return 0;
+}
+
+// SignedDigitDecompose of a 2-component ciphertext (COEFFICIENT values) -> out [digitsG2][N]
+int ref_decompose(void* hv, const uint64_t* in, uint64_t* out) {
+    auto* h     = static_cast<RefCtx*>(hv);
+    auto rgsw   = h->cc.GetParams()->GetRingGSWParams();
+    auto pp     = rgsw->GetPolyParams();
+    uint32_t N  = rgsw->GetN();
+    uint32_t d2 = (rgsw->GetDigitsG() - 1) << 1;
+    std::vector<NativePoly> ct(2, NativePoly(pp, Format::COEFFICIENT, true));
+    for (int c = 0; c < 2; ++c)
+        for (uint32_t k = 0; k < N; ++k)
+            ct[c][k] = NativeInteger(in[c * N + k]);
+    std::vector<NativePoly> dct(d2, NativePoly(pp, Format::COEFFICIENT, true));
+    RingGSWAccumulatorCGGI().SignedDigitDecompose(rgsw, ct, dct);
+    for (uint32_t d = 0; d < d2; ++d)
+        for (uint32_t k = 0; k < N; ++k)
+            out[d * N + k] = dct[d][k].ConvertToInt();
+    return 0;
+}
+
+// LWE ModSwitch / KeySwitch on flat data (lwe-pke.cpp:254-261, :348-372)
+int ref_modswitch(void* hv, uint64_t qto, uint64_t qfrom, const uint64_t* a, const uint64_t* b, uint64_t* oa,
+                  uint64_t* ob, uint32_t len, uint64_t count) {
+    auto* h = static_cast<RefCtx*>(hv);
+    for (uint64_t i = 0; i < count; ++i) {
+        auto c = make_ct(a + i * len, b[i], len, qfrom);
+        auto r = h->cc.GetLWEScheme()->ModSwitch(NativeInteger(qto), c);
+        put_ct(r, oa + i * len, ob + i);
+    }
+    return 0;
+}
+
+int ref_keyswitch(void* hv, const uint64_t* a, const uint64_t* b, uint64_t* oa, uint64_t* ob, uint64_t count) {
+    auto* h    = static_cast<RefCtx*>(hv);
+    auto lwe   = h->cc.GetParams()->GetLWEParams();
+    uint32_t N = lwe->GetN(), n = lwe->Getn();
+    for (uint64_t i = 0; i < count; ++i) {
+        auto c = make_ct(a + i * N, b[i], N, lwe->GetqKS().ConvertToInt());
+        auto r = h->cc.GetLWEScheme()->KeySwitch(lwe, h->cc.GetSwitchKey(), c);
+        put_ct(r, oa + i * n, ob + i);
+    }
+    return 0;
+}
+
+// ---- NTT (NativePoly::SwitchFormat path) -------------------------------------------------------
+uint64_t ref_root_of_unity(uint64_t m, uint64_t Q) {
+    return RootOfUnity<NativeInteger>(static_cast<usint>(m), NativeInteger(Q)).ConvertToInt();
+}
+
+uint64_t ref_last_prime(uint32_t bits, uint64_t m) {
+    return LastPrime<NativeInteger>(bits, m).ConvertToInt();
+}
+
+uint64_t ref_previous_prime(uint64_t q, uint64_t m) {
+    return PreviousPrime<NativeInteger>(NativeInteger(q), m).ConvertToInt();
+}
+
+// data [count][N], in place. inverse=0: ForwardTransformToBitReverseInPlace, 1: InverseTransformFromBitReverseInPlace
+int ref_ntt(uint64_t Q, uint64_t psi, uint32_t N, uint64_t* data, uint64_t count, int inverse, int threads) {
+    NativeInteger mod(Q), root(psi);
+    // fill the process-global tables once, single-threaded (transformnat-impl.h:777-831)
+    {
+        NativeVector v(N, mod);
+        ChineseRemainderTransformFTT<NativeVector>().ForwardTransformToBitReverseInPlace(root, 2 * N, &v);
+        ChineseRemainderTransformFTT<NativeVector>().InverseTransformFromBitReverseInPlace(root, 2 * N, &v);
+    }
+#pragma omp parallel for num_threads(threads > 0 ? threads : 1)
+    for (uint64_t i = 0; i < count; ++i) {
+        NativeVector v(N, mod);
+        uint64_t* p = data + i * N;
+        for (uint32_t k = 0; k < N; ++k)
+            v[k] = NativeInteger(p[k]);
+        if (inverse)
+            ChineseRemainderTransformFTT<NativeVector>().InverseTransformFromBitReverseInPlace(root, 2 * N, &v);
+        else
+            ChineseRemainderTransformFTT<NativeVector>().ForwardTransformToBitReverseInPlace(root, 2 * N, &v);
+        for (uint32_t k = 0; k < N; ++k)
+            p[k] = v[k].ConvertToInt();
+    }
+    return 0;
+}
+
+// Moduli chain of ILDCRTParams(order=2N, depth=L, bits) (ildcrtparams.h:100-118): q[L], psi[L]
+int ref_dcrt_chain(uint32_t N, uint32_t L, uint32_t bits, uint64_t* q, uint64_t* psi) {
+    ILDCRTParams<BigInteger> p(2 * N, L, bits);
+    for (uint32_t l = 0; l < L; ++l) {
+        q[l]   = p.GetParams()[l]->GetModulus().ConvertToInt();
+        psi[l] = p.GetParams()[l]->GetRootOfUnity().ConvertToInt();
+    }
+    return 0;
+}
+
+// DCRTPoly::SwitchFormat on flat data [count][L][N] (dcrtpoly-impl.h:1953-1959), in place.
+// fmt_in: 0 = COEFFICIENT (forward NTT), 1 = EVALUATION (inverse NTT)
+int ref_dcrt_switchformat(uint32_t N, uint32_t L, uint32_t bits, uint64_t* data, uint64_t count, int fmt_in) {
+    auto params = std::make_shared<ILDCRTParams<BigInteger>>(2 * N, L, bits);
+    for (uint64_t i = 0; i < count; ++i) {
+        DCRTPoly poly(params, fmt_in ? Format::EVALUATION : Format::COEFFICIENT, true);
+        for (uint32_t l = 0; l < L; ++l) {
+            NativePoly limb = poly.GetElementAtIndex(l);
+            uint64_t* p     = data + (i * L + l) * N;
+            for (uint32_t k = 0; k < N; ++k)
+                limb[k] = NativeInteger(p[k]);
+            poly.SetElementAtIndex(l, std::move(limb));
+        }
+        poly.SwitchFormat();
+        for (uint32_t l = 0; l < L; ++l) {
+            const NativePoly& limb = poly.GetElementAtIndex(l);
+            uint64_t* p            = data + (i * L + l) * N;
+            for (uint32_t k = 0; k < N; ++k)
+                p[k] = limb[k].ConvertToInt();
+        }
+    }
+    return 0;
+}
+
+// ---- CPU baseline timers (bench.py --impl reference / cpu_baseline) --------------------------------
+// `count` EvalBinGate(gate) on count ciphertext pairs, outer OMP loop over independent gates — the shape
+// of EvalBinGateBatch (src/binfhe/lib/batch/batch.cpp:197-200). Returns seconds.
+double ref_time_bingate(void* hv, int gate, const uint64_t* a1, const uint64_t* b1, const uint64_t* a2,
+                        const uint64_t* b2, uint64_t* oa, uint64_t* ob, uint64_t count, int threads) {
+    omp_set_max_active_levels(1);
+    auto t0 = std::chrono::steady_clock::now();
+    ref_evalbingate(hv, gate, a1, b1, a2, b2, oa, ob, count, 0, threads);
+    auto t1 = std::chrono::steady_clock::now();
+    return std::chrono::duration<double>(t1 - t0).count();
+}
+
+double ref_time_ntt(uint64_t Q, uint64_t psi, uint32_t N, uint64_t* data, uint64_t count, int inverse,
+                    int threads) {
+    // warm tables
+    ref_ntt(Q, psi, N, data, 1, 0, 1);
+    ref_ntt(Q, psi, N, data, 1, 1, 1);
+    NativeInteger mod(Q), root(psi);
+    std::vector<NativeVector> vs;
+    vs.reserve(count);
+    for (uint64_t i = 0; i < count; ++i) {
+        NativeVector v(N, mod);
+        for (uint32_t k = 0; k < N; ++k)
+            v[k] = NativeInteger(data[i * N + k]);
+        vs.push_back(std::move(v));
+    }
+    auto t0 = std::chrono::steady_clock::now();
+#pragma omp parallel for num_threads(threads > 0 ? threads : 1)
+    for (uint64_t i = 0; i < count; ++i) {
+        if (inverse)
+            ChineseRemainderTransformFTT<NativeVector>().InverseTransformFromBitReverseInPlace(root, 2 * N, &vs[i]);
+        else
+            ChineseRemainderTransformFTT<NativeVector>().ForwardTransformToBitReverseInPlace(root, 2 * N, &vs[i]);
+    }
+    auto t1 = std::chrono::steady_clock::now();
+    for (uint64_t i = 0; i < count; ++i)
+        for (uint32_t k = 0; k < N; ++k)
+            data[i * N + k] = vs[i][k].ConvertToInt();
+    return std::chrono::duration<double>(t1 - t0).count();
+}
+
+int ref_max_threads() {
+    return omp_get_max_threads();
+}
+
+}  // extern "C"
