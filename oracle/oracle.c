@@ -766,6 +766,10 @@ static int evalfunc_one(OrcCtx* c, const u64* a, u64 b, const u64* LUT, u64 lutl
         for (u64 x = 0; x < wm; ++x) f2[x] = x < (wm >> 1) ? LUT[x] : wm - LUT[x - wm / 2];
     }
     bootstrap_func(c, a3, b3, wm, f2, wm, oa, ob);
+    if (prop == 2) { /* ct4->SetModulus(q): lwe-ciphertext.h:116-120 reduces a and b mod q */
+        for (u32 i = 0; i < n; ++i) oa[i] %= q;
+        *ob %= q;
+    }
     free(a3); free(f);
     return 0;
 }
