@@ -1,0 +1,240 @@
+"""Host-side mirror of the reference's batch interface over libluxb200.so.
+
+Names and semantics follow the reference so that parity tests read like its own:
+  BinFHEContext.GenerateBinFHEContext(set, method)      src/binfhe/lib/binfhecontext.cpp:109-187 (parameter table :113-159)
+  BinFHEContext.BTKeyLoad(keys)                          src/binfhe/include/binfhecontext.h:273
+  EvalBinGateBatch / BootstrapBatch / EvalFuncBatch / EvalCMUXBatch / KeySwitchBatch / ModSwitchBatch
+                                                         src/binfhe/include/batch/binfhe-batch.h:48-174
+  BatchResult{success, processed, failed, error}         binfhe-batch.h:29-40
+  BlindRotateBatch                                       src/binfhe/include/backend/backend.h:177-183
+Ciphertext batches are flat arrays: a [count][n] uint64, b [count] uint64 (NativeVector element type).
+Key generation stays with the caller (the reference's BTKeyGen, or fhe_b200.keygen for synthetic keys).
+"""
+import ctypes as C
+from dataclasses import dataclass
+
+import numpy as np
+
+from . import lib as _l
+
+PRIME = 0
+# { name: (numberBits, cyclOrder, latticeParam n, mod q, modKS, baseKS, gadgetBase, baseRK, numAutoKeys, keyDist) }
+# binfhecontext.cpp:117-158 (keyDist: 0 = UNIFORM_TERNARY, 1 = GAUSSIAN)
+PARAM_SETS = {
+    "TOY": (27, 1024, 64, 512, PRIME, 25, 512, 23, 9, 0),
+    "MEDIUM": (28, 2048, 422, 1024, 16384, 128, 1024, 32, 10, 0),
+    "STD128_AP": (27, 2048, 503, 1024, 16384, 32, 512, 32, 10, 0),
+    "STD128": (27, 2048, 503, 1024, 16384, 32, 512, 32, 10, 0),
+    "STD128_3": (27, 2048, 595, 1024, 65536, 64, 128, 32, 10, 0),
+    "STD128_4": (27, 2048, 595, 2048, 65536, 64, 128, 64, 10, 0),
+    "STD128Q": (25, 2048, 534, 1024, 16384, 32, 128, 32, 10, 0),
+    "STD128_LMKCDEY": (28, 2048, 447, 2048, 16384, 32, 1024, 64, 10, 1),
+    "STD128_3_LMKCDEY": (27, 2048, 556, 2048, 32768, 32, 512, 64, 10, 0),
+    "STD128Q_LMKCDEY": (27, 2048, 483, 2048, 16384, 32, 512, 64, 10, 1),
+    "LPF_STD128": (27, 2048, 556, 2048, 32768, 32, 128, 64, 10, 0),
+    "LPF_STD128_LMKCDEY": (27, 2048, 556, 2048, 32768, 32, 512, 64, 10, 0),
+    "SIGNED_MOD_TEST": (28, 2048, 512, 1024, PRIME, 25, 128, 23, 10, 0),
+}
+
+
+@dataclass
+class BatchResult:
+    success: bool = True
+    processed: int = 0
+    failed: int = 0
+    error: str = ""
+
+
+class BinFHEContext:
+    """Device-side counterpart of lux::fhe::BinFHEContext for the batched hot path (one context = one GPU)."""
+
+    def __init__(self, device=0):
+        self.L = _l.load()
+        self.device = device
+        self.h = None
+        self.info = None
+
+    # -- parameters ---------------------------------------------------------------------------------------
+    def GenerateBinFHEContext(self, paramset, method="GINX"):
+        if paramset not in PARAM_SETS:
+            raise _l.LuxB200Error(-4, f"unknown parameter set {paramset}")
+        bits, cyc, n, q, modKS, baseKS, baseG, baseR, nauto, keyDist = PARAM_SETS[paramset]
+        Q = self.L.luxb200_last_prime(bits, cyc)
+        self.keyDist = keyDist
+        return self.GenerateFromParams(n=n, N=cyc // 2, q=q, Q=Q, qKS=(Q if modKS == PRIME else modKS), baseKS=baseKS,
+                                       baseG=baseG, baseR=baseR, numAutoKeys=nauto, method=method)
+
+    def GenerateFromParams(self, n, N, q, Q, qKS, baseKS, baseG, baseR, numAutoKeys, method, psi=0):
+        self.close()
+        p = _l.Params(n=n, N=N, q=q, Q=Q, qKS=qKS, baseKS=baseKS, baseG=baseG, baseR=baseR, numAutoKeys=numAutoKeys,
+                      method=_l.METHOD[method] if isinstance(method, str) else int(method), reserved=0, psi=psi)
+        h = _l.VP()
+        _l.check(self.L.luxb200_ctx_create(C.byref(p), self.device, C.byref(h)))
+        self.h = h
+        arr = np.zeros(16, np.uint64)
+        _l.check(self.L.luxb200_ctx_info(self.h, _l.ptr(arr)))
+        names = ["n", "N", "q", "Q", "qKS", "baseKS", "baseG", "baseR", "digitsG", "numAutoKeys", "_", "psi", "digitsKS",
+                 "method", "digitsR", "device"]
+        for k, v in zip(names, arr):
+            setattr(self, k, int(v))
+        self.rows = 2 * (self.digitsG - 1)
+        return self
+
+    def GetBeta(self):
+        return 128  # binfhecontext.h:445-447
+
+    def bsk_len(self):
+        return int(self.L.luxb200_bsk_len(self.h))
+
+    def ksk_rows(self):
+        return self.N * self.baseKS * self.digitsKS
+
+    # -- keys -----------------------------------------------------------------------------------------------
+    def BTKeyLoad(self, bsk, kskA, kskB, on_device=False):
+        """bsk / kskA / kskB: canonical flat uint64 arrays (numpy) or device pointers (ints) when on_device."""
+        _l.check(self.L.luxb200_load_bsk(self.h, _l.ptr(bsk), int(on_device)))
+        _l.check(self.L.luxb200_load_ksk(self.h, _l.ptr(kskA), _l.ptr(kskB), int(on_device)))
+
+    # -- batched operators (host buffers) -----------------------------------------------------------------
+    def _u64(self, x):
+        return np.ascontiguousarray(x, dtype=np.uint64)
+
+    def EvalBinGateBatch(self, gate, ct1, ct2, extended=False):
+        (a1, b1), (a2, b2) = ct1, ct2
+        a1, b1, a2, b2 = map(self._u64, (a1, b1, a2, b2))
+        cnt = len(b1)
+        oa = np.empty((cnt, self.N if extended else self.n), np.uint64)
+        ob = np.empty(cnt, np.uint64)
+        rc = self.L.luxb200_evalbingate_batch(self.h, _l.GATE[gate], _l.ptr(a1), _l.ptr(b1), _l.ptr(a2), _l.ptr(b2),
+                                              _l.ptr(oa), _l.ptr(ob), cnt, int(extended))
+        return (oa, ob), self._result(rc, cnt)
+
+    def EvalBinGateMultiBatch(self, gate, a, b, p=4):
+        a, b = self._u64(a), self._u64(b)
+        cnt, k = b.shape
+        oa = np.empty((cnt, self.n), np.uint64)
+        ob = np.empty(cnt, np.uint64)
+        rc = self.L.luxb200_evalbingate_multi_batch(self.h, _l.GATE[gate], k, _l.ptr(a), _l.ptr(b), _l.ptr(oa),
+                                                    _l.ptr(ob), cnt, p)
+        return (oa, ob), self._result(rc, cnt)
+
+    def EvalCMUXBatch(self, ct_true, ct_false, ct_sel):
+        """EvalCMUXBatch(sel, ct_true, ct_false) of binfhe-batch.h:113-125 = EvalBinGate(CMUX, {ct1, ct2, sel})."""
+        a = np.stack([self._u64(ct_true[0]), self._u64(ct_false[0]), self._u64(ct_sel[0])], axis=1)
+        b = np.stack([self._u64(ct_true[1]), self._u64(ct_false[1]), self._u64(ct_sel[1])], axis=1)
+        return self.EvalBinGateMultiBatch("CMUX", a, b)
+
+    def BootstrapBatch(self, ct, p=4, extended=False):
+        a, b = map(self._u64, ct)
+        cnt = len(b)
+        oa = np.empty((cnt, self.N if extended else self.n), np.uint64)
+        ob = np.empty(cnt, np.uint64)
+        rc = self.L.luxb200_bootstrap_batch(self.h, _l.ptr(a), _l.ptr(b), _l.ptr(oa), _l.ptr(ob), cnt, p, int(extended))
+        return (oa, ob), self._result(rc, cnt)
+
+    def EvalFuncBatch(self, ct, lut, ctmod=None):
+        a, b = map(self._u64, ct)
+        lut = self._u64(lut)
+        cnt = len(b)
+        oa = np.empty((cnt, self.n), np.uint64)
+        ob = np.empty(cnt, np.uint64)
+        rc = self.L.luxb200_evalfunc_batch(self.h, _l.ptr(a), _l.ptr(b), _l.ptr(lut), len(lut), self.GetBeta(),
+                                           _l.ptr(oa), _l.ptr(ob), cnt, ctmod or self.q)
+        return (oa, ob), self._result(rc, cnt)
+
+    def BlindRotateBatch(self, a, acc, amod=None):
+        a = self._u64(a)
+        acc = self._u64(acc).copy()
+        _l.check(self.L.luxb200_blind_rotate_batch(self.h, _l.ptr(a), amod or self.q, _l.ptr(acc), a.shape[0]))
+        return acc
+
+    def KeySwitchBatch(self, ct):
+        a, b = map(self._u64, ct)
+        cnt = len(b)
+        oa = np.empty((cnt, self.n), np.uint64)
+        ob = np.empty(cnt, np.uint64)
+        _l.check(self.L.luxb200_keyswitch_batch(self.h, _l.ptr(a), _l.ptr(b), _l.ptr(oa), _l.ptr(ob), cnt))
+        return oa, ob
+
+    def ModSwitchBatch(self, x, qto, qfrom):
+        x = self._u64(x)
+        out = np.empty_like(x)
+        _l.check(self.L.luxb200_modswitch_batch(self.h, qto, qfrom, _l.ptr(x), _l.ptr(out), x.size))
+        return out
+
+    def GenerateLUTviaFunction(self, f, p):
+        """binfhecontext.cpp:372-387"""
+        q = self.q
+        out = np.zeros(q, np.uint64)
+        for i in range(q):
+            v = (q // p) * f((i * p) // q, p)
+            if v >= q:
+                raise ValueError("input function should output in Z_{p_output}")
+            out[i] = v
+        return out
+
+    # -- device-resident operators (uint32 tensors already in HBM; pointers as ints) ------------------------
+    def EvalBinGateBatchDev(self, gate, a1, b1, a2, b2, oa, ob, count):
+        _l.check(self.L.luxb200_evalbingate_batch_dev(self.h, _l.GATE[gate], _l.VP(a1), _l.VP(b1), _l.VP(a2), _l.VP(b2),
+                                                      _l.VP(oa), _l.VP(ob), count))
+
+    def Synchronize(self):
+        _l.check(self.L.luxb200_synchronize(self.h))
+
+    def LastTiming(self):
+        t = np.zeros(8, np.float32)
+        _l.check(self.L.luxb200_last_timing(self.h, _l.ptr(t)))
+        return {"prep_ms": float(t[0]), "br_ms": float(t[1]), "ks_ms": float(t[2]), "total_ms": float(t[3]),
+                "launches": int(t[4])}
+
+    def LaunchCount(self):
+        return int(self.L.luxb200_launch_count(self.h))
+
+    def _result(self, rc, cnt):
+        if rc == 0:
+            return BatchResult(True, cnt, 0, "")
+        return BatchResult(False, 0, cnt, self.L.luxb200_last_error().decode())
+
+    def close(self):
+        if self.h:
+            self.L.luxb200_ctx_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+class NTTPlan:
+    """PolyImpl::SwitchFormat / DCRTPolyImpl::SwitchFormat on flat [count][L][N] data."""
+
+    def __init__(self, N, moduli, roots=None, device=0):
+        self.L = _l.load()
+        q = np.ascontiguousarray(moduli, np.uint64)
+        psi = np.ascontiguousarray(roots, np.uint64) if roots is not None else None
+        h = _l.VP()
+        _l.check(self.L.luxb200_ntt_plan_create(N, len(q), _l.ptr(q), _l.ptr(psi) if psi is not None else None, device,
+                                                C.byref(h)))
+        self.h, self.N, self.nl = h, N, len(q)
+
+    def SwitchFormat(self, data, inverse):
+        data = np.ascontiguousarray(data, np.uint64).copy()
+        count = data.size // (self.N * self.nl)
+        _l.check(self.L.luxb200_ntt_batch(self.h, _l.ptr(data), count, int(inverse)))
+        return data
+
+    def SwitchFormatDev(self, dptr, count, inverse, elem_bytes):
+        _l.check(self.L.luxb200_ntt_batch_dev(self.h, _l.VP(dptr), count, int(inverse), elem_bytes))
+
+    def Sync(self):
+        _l.check(self.L.luxb200_ntt_plan_sync(self.h))
+
+    def LastMs(self):
+        return float(self.L.luxb200_ntt_last_ms(self.h))
+
+    def close(self):
+        if self.h:
+            self.L.luxb200_ntt_plan_destroy(self.h)
+            self.h = None

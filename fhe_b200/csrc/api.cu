@@ -1,0 +1,292 @@
+// api.cu — C ABI of libluxb200.so (see include/luxb200.h for the reference interfaces each entry replaces).
+#include "api_common.h"
+#include "aux_kernels.cuh"
+#include "br_kernels.cuh"
+#include "ntt_kernels.cuh"
+
+thread_local std::string g_last_error;
+
+int lb_fail(int code, const char* fmt, ...) {
+    char buf[512];
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(buf, sizeof(buf), fmt, ap);
+    va_end(ap);
+    g_last_error = buf;
+    return code;
+}
+int lb_set_device(int device) {
+    int cnt = 0;
+    cudaError_t e = cudaGetDeviceCount(&cnt);
+    if (e != cudaSuccess || cnt == 0)
+        return lb_fail(LUXB200_ERR_NO_DEVICE, "no CUDA device available (%s); libluxb200 has no CPU fallback",
+                       e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+    if (device < 0 || device >= cnt) return lb_fail(LUXB200_ERR_INVALID_ARG, "device %d out of range [0,%d)", device, cnt);
+    LB_CUDA(cudaSetDevice(device));
+    return 0;
+}
+static inline unsigned nblk(uint64_t total, unsigned bs) { return (unsigned)((total + bs - 1) / bs); }
+
+// ---- u32 NTT tables -------------------------------------------------------------------------------------------
+int Ntt32Tables::build(uint32_t N_, uint64_t Q_, uint64_t psi_) {
+    using namespace lb;
+    N = N_; Q = Q_; psi = psi_;
+    logN = ilog2(N);
+    if (Q >= (1ull << 30)) return lb_fail(LUXB200_ERR_UNSUPPORTED, "u32 NTT path needs Q < 2^30 (got %llu)", (unsigned long long)Q);
+    logH = 32 - bits_of(Q);
+    if (logH > 5) logH = 5;
+    std::vector<uint64_t> tw, twi;
+    ntt_tables(N, Q, psi, tw, twi);
+    const uint32_t E = N / 32, TB = (E / 2 < 16) ? E / 2 : 16;
+    memset(&C, 0, sizeof(C));
+    for (uint32_t i = 1; i < E && i < 64; ++i) {
+        C.twA[i]  = make_uint2((u32)tw[i], shoup32(tw[i], Q));
+        C.twiA[i] = make_uint2((u32)twi[i], shoup32(twi[i], Q));
+    }
+    C.Q = (u32)Q; C.Q2 = (u32)(2 * Q); C.mu32 = (u32)((1ull << 32) / Q);
+    uint64_t ninv = invmod_prime(N % Q, Q);
+    C.ninv = (u32)ninv; C.ninv_s = shoup32(ninv, Q);
+    uint64_t w1 = mulmod(twi[1], ninv, Q);
+    C.w1ninv = (u32)w1; C.w1ninv_s = shoup32(w1, Q);
+    // lane-major phase-B tables
+    std::vector<uint2> hB, hBi, hF(N), hFi(N);
+    uint32_t off = 0;
+    for (uint32_t t = TB; t >= 1; t >>= 1) {
+        const uint32_t g = E / (2 * t);
+        hB.resize((off + g) * 32);
+        hBi.resize((off + g) * 32);
+        for (uint32_t i = 0; i < g; ++i)
+            for (uint32_t lane = 0; lane < 32; ++lane) {
+                const uint32_t idx = N / (2 * t) + g * lane + i;
+                hB[(off + i) * 32 + lane]  = make_uint2((u32)tw[idx], shoup32(tw[idx], Q));
+                hBi[(off + i) * 32 + lane] = make_uint2((u32)twi[idx], shoup32(twi[idx], Q));
+            }
+        off += g;
+    }
+    for (uint32_t i = 0; i < N; ++i) {
+        hF[i]  = make_uint2((u32)tw[i], shoup32(tw[i], Q));
+        hFi[i] = make_uint2((u32)twi[i], shoup32(twi[i], Q));
+    }
+    LB_TRY(twB.ensure(hB.size() * sizeof(uint2)));
+    LB_TRY(twiB.ensure(hBi.size() * sizeof(uint2)));
+    LB_TRY(twfull.ensure(N * sizeof(uint2)));
+    LB_TRY(twifull.ensure(N * sizeof(uint2)));
+    LB_CUDA(cudaMemcpy(twB.p, hB.data(), hB.size() * sizeof(uint2), cudaMemcpyHostToDevice));
+    LB_CUDA(cudaMemcpy(twiB.p, hBi.data(), hBi.size() * sizeof(uint2), cudaMemcpyHostToDevice));
+    LB_CUDA(cudaMemcpy(twfull.p, hF.data(), N * sizeof(uint2), cudaMemcpyHostToDevice));
+    LB_CUDA(cudaMemcpy(twifull.p, hFi.data(), N * sizeof(uint2), cudaMemcpyHostToDevice));
+    return 0;
+}
+
+extern "C" {
+
+const char* luxb200_last_error(void) { return g_last_error.c_str(); }
+int luxb200_version(void) { return 100; }
+int luxb200_device_count(void) {
+    int cnt = 0;
+    if (cudaGetDeviceCount(&cnt) != cudaSuccess) return 0;
+    return cnt;
+}
+uint64_t luxb200_last_prime(uint32_t bits, uint64_t m) { return lb::last_prime(bits, m); }
+uint64_t luxb200_previous_prime(uint64_t q, uint64_t m) { return lb::previous_prime(q, m); }
+uint64_t luxb200_root_of_unity(uint64_t m, uint64_t q) { return lb::root_of_unity(m, q); }
+
+int luxb200_ctx_create(const luxb200_params* p, int device, luxb200_ctx** out) {
+    using namespace lb;
+    if (!p || !out) return lb_fail(LUXB200_ERR_INVALID_ARG, "null argument");
+    *out = nullptr;
+    if (p->N < 256 || (p->N & (p->N - 1))) return lb_fail(LUXB200_ERR_INVALID_ARG, "N must be a power of two >= 256");
+    if (p->method < LUXB200_AP || p->method > LUXB200_LMKCDEY) return lb_fail(LUXB200_ERR_INVALID_ARG, "bad method %u", p->method);
+    if (p->baseG == 0 || (p->baseG & (p->baseG - 1))) return lb_fail(LUXB200_ERR_INVALID_ARG, "Gadget base should be a power of two.");
+    if (p->q == 0 || (p->q & (p->q - 1)) || (2ull * p->N) % p->q) return lb_fail(LUXB200_ERR_INVALID_ARG, "q must be a power of two dividing 2N");
+    if (p->Q >= (1ull << 30) || !is_prime(p->Q) || (p->Q - 1) % (2ull * p->N))
+        return lb_fail(LUXB200_ERR_UNSUPPORTED, "Q must be an NTT prime below 2^30 on the u32 bootstrapping path");
+    if (p->qKS >= (1ull << 32)) return lb_fail(LUXB200_ERR_UNSUPPORTED, "qKS must fit in 32 bits");
+    if (p->N > 1024) return lb_fail(LUXB200_ERR_UNSUPPORTED, "blind rotation kernels are built for N <= 1024 (got %u)", p->N);
+    LB_TRY(lb_set_device(device));
+    luxb200_ctx* c = new luxb200_ctx();
+    c->p = *p;
+    c->device = device;
+    c->logN = ilog2(p->N);
+    c->digitsG = digit_count(p->Q, p->baseG);
+    c->digitsKS = digit_count(p->qKS, p->baseKS);
+    c->digitsR = digit_count(p->q, p->baseR ? p->baseR : 2);
+    c->rows = 2 * (c->digitsG - 1);
+    if (c->p.psi == 0) c->p.psi = root_of_unity(2ull * p->N, p->Q);
+    if (c->rows != 4 && c->rows != 6 && c->rows != 2) { delete c; return lb_fail(LUXB200_ERR_UNSUPPORTED, "digitsG-1 = %u not supported", c->rows / 2); }
+    // reduce64 constants: x < max(rows * 2Q * Q, 8 Q^2 + 4Q)
+    {
+        u128_t Q = p->Q, xmax = (u128_t)c->rows * 2 * Q * Q;
+        u128_t alt = 8 * Q * Q + 4 * Q;
+        if (alt > xmax) xmax = alt;
+        uint32_t b = 0;
+        while ((xmax >> b) != 0) ++b;
+        uint32_t s = b > 32 ? b - 32 : 0;
+        if (s > bits_of(p->Q) - 1) { delete c; return lb_fail(LUXB200_ERR_UNSUPPORTED, "Q too large for the 64->32 reduction (rows=%u)", c->rows); }
+        c->red_s = s;
+        c->red_mu = (uint32_t)((((u128_t)1) << (s + 32)) / Q);
+    }
+    int rc = c->ntt.build(p->N, p->Q, c->p.psi);
+    if (rc) { delete c; return rc; }
+    cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
+    for (int i = 0; i < 5 && e == cudaSuccess; ++i) e = cudaEventCreate(&c->ev[i]);
+    if (e != cudaSuccess) { delete c; return lb_fail(LUXB200_ERR_CUDA, "stream/event creation failed: %s", cudaGetErrorString(e)); }
+    if (p->method == LUXB200_GINX) {
+        // monomials X^a - 1 in EVALUATION format (rgsw-cryptoparameters.cpp:96-113), sigma order:
+        // value at index p is psi^(a (2 brv(p) + 1)) - 1
+        const uint32_t N = p->N, M = 2 * N, E = N / 32;
+        std::vector<uint64_t> pw(M);
+        pw[0] = 1;
+        for (uint32_t i = 1; i < M; ++i) pw[i] = mulmod(pw[i - 1], c->p.psi, p->Q);
+        std::vector<u32> h((size_t)M * N);
+        std::vector<uint32_t> odd(N);
+        for (uint32_t pp = 0; pp < N; ++pp) odd[pp] = 2 * bitrev(pp, c->logN) + 1;
+        for (uint32_t a = 0; a < M; ++a)
+            for (uint32_t pp = 0; pp < N; ++pp) {
+                const uint32_t l = pp / E, r = pp % E;
+                const uint64_t v = pw[((uint64_t)a * odd[pp]) % M];
+                h[(size_t)a * N + (r >> 2) * 128 + 4 * l + (r & 3)] = (u32)(v ? v - 1 : p->Q - 1);
+            }
+        rc = c->mono.ensure(h.size() * 4);
+        if (!rc && cudaMemcpy(c->mono.p, h.data(), h.size() * 4, cudaMemcpyHostToDevice) != cudaSuccess)
+            rc = lb_fail(LUXB200_ERR_CUDA, "mono upload failed");
+        if (rc) { luxb200_ctx_destroy(c); return rc; }
+    }
+    if (p->method == LUXB200_LMKCDEY) {
+        // EVALUATION-format automorphism maps (PrecomputeAutoMap, nbtheory2.cpp:264-275) for k = 2N-5, 5^1..5^w,
+        // as gather indices in sigma order: out[sigma(p)] = in[sigma(map[p])]
+        const uint32_t N = p->N, M = 2 * N, E = N / 32, w = p->numAutoKeys;
+        std::vector<u32> h((size_t)(w + 1) * N);
+        for (uint32_t t = 0; t <= w; ++t) {
+            uint32_t k = (t == 0) ? M - 5 : (uint32_t)powmod(5, t, M);
+            for (uint32_t j = 0; j < N; ++j) {
+                uint32_t jt = 2 * j + 1;
+                uint32_t idx = (uint32_t)(((uint64_t)jt * k) % M) >> 1;
+                uint32_t dst = bitrev(j, c->logN), src = bitrev(idx, c->logN);
+                uint32_t ld = dst / E, rd = dst % E;
+                h[(size_t)t * N + (rd >> 2) * 128 + 4 * ld + (rd & 3)] = src;  // natural EVAL index of the source
+            }
+        }
+        rc = c->automap.ensure(h.size() * 4);
+        if (!rc && cudaMemcpy(c->automap.p, h.data(), h.size() * 4, cudaMemcpyHostToDevice) != cudaSuccess)
+            rc = lb_fail(LUXB200_ERR_CUDA, "automap upload failed");
+        if (rc) { luxb200_ctx_destroy(c); return rc; }
+    }
+    // KSK element type
+    c->ks_elem = (p->qKS <= 65536) ? 2 : 4;
+    c->npad = (p->n + 7) & ~7u;
+    *out = c;
+    return 0;
+}
+
+void luxb200_ctx_destroy(luxb200_ctx* c) {
+    if (!c) return;
+    cudaSetDevice(c->device);
+    DevBuf* bufs[] = {&c->bsk, &c->mono, &c->kskA, &c->kskB, &c->automap, &c->in0, &c->in1, &c->in2, &c->in3, &c->wa,
+                      &c->wb, &c->lut, &c->ext, &c->oa, &c->ob, &c->o64a, &c->o64b, &c->sched, &c->tmpa, &c->tmpb,
+                      &c->tmpc, &c->tmpd};
+    for (DevBuf* b : bufs) b->release();
+    c->ntt.release();
+    for (int i = 0; i < 5; ++i)
+        if (c->ev[i]) cudaEventDestroy(c->ev[i]);
+    if (c->stream) cudaStreamDestroy(c->stream);
+    delete c;
+}
+
+int luxb200_ctx_info(luxb200_ctx* c, uint64_t* o) {
+    if (!c || !o) return lb_fail(LUXB200_ERR_INVALID_ARG, "null argument");
+    o[0] = c->p.n; o[1] = c->p.N; o[2] = c->p.q; o[3] = c->p.Q; o[4] = c->p.qKS; o[5] = c->p.baseKS; o[6] = c->p.baseG;
+    o[7] = c->p.baseR; o[8] = c->digitsG; o[9] = c->p.numAutoKeys; o[10] = 0; o[11] = c->p.psi; o[12] = c->digitsKS;
+    o[13] = c->p.method; o[14] = c->digitsR; o[15] = (uint64_t)c->device;
+    return 0;
+}
+
+uint64_t luxb200_bsk_len(luxb200_ctx* c) {
+    if (!c) return 0;
+    const uint64_t rg = (uint64_t)c->rows * 2 * c->p.N;
+    if (c->p.method == LUXB200_GINX) return (uint64_t)c->p.n * 2 * rg;
+    if (c->p.method == LUXB200_AP) return (uint64_t)c->p.n * c->p.baseR * c->digitsR * rg;
+    return (uint64_t)c->p.n * rg + (uint64_t)(c->p.numAutoKeys + 1) * (c->digitsG - 1) * 2 * c->p.N;
+}
+uint64_t luxb200_ksk_len(luxb200_ctx* c) {
+    if (!c) return 0;
+    return (uint64_t)c->p.N * c->p.baseKS * c->digitsKS * c->p.n;
+}
+
+int luxb200_load_bsk(luxb200_ctx* c, const uint64_t* bsk, int on_device) {
+    if (!c || !bsk) return lb_fail(LUXB200_ERR_INVALID_ARG, "null argument");
+    LB_TRY(lb_set_device(c->device));
+    const uint64_t len = luxb200_bsk_len(c);
+    LB_TRY(c->bsk.ensure(len * 4));
+    // stream the canonical u64 key through a bounded staging buffer
+    const uint64_t chunk = (uint64_t)c->p.N * 4096;  // polynomials are N-aligned
+    DevBuf stage;
+    if (!on_device) LB_TRY(stage.ensure(std::min(len, chunk) * 8));
+    for (uint64_t off = 0; off < len; off += chunk) {
+        const uint64_t m = std::min(chunk, len - off);
+        const u64* src = bsk + off;
+        if (!on_device) {
+            LB_CUDA(cudaMemcpyAsync(stage.p, bsk + off, m * 8, cudaMemcpyHostToDevice, c->stream));
+            src = stage.as<u64>();
+        }
+        pack_polys_sigma_kernel<<<nblk(m, 256), 256, 0, c->stream>>>(src, c->bsk.as<u32>() + off, c->logN, m);
+        c->launches++;
+    }
+    LB_CUDA(cudaStreamSynchronize(c->stream));
+    stage.release();
+    c->have_bsk = true;
+    return 0;
+}
+
+int luxb200_load_ksk(luxb200_ctx* c, const uint64_t* A, const uint64_t* B, int on_device) {
+    if (!c || !A || !B) return lb_fail(LUXB200_ERR_INVALID_ARG, "null argument");
+    LB_TRY(lb_set_device(c->device));
+    const uint64_t rows = (uint64_t)c->p.N * c->p.baseKS * c->digitsKS;
+    LB_TRY(c->kskA.ensure(rows * c->npad * c->ks_elem));
+    LB_TRY(c->kskB.ensure(rows * 4));
+    const uint64_t chunk_rows = 65536;
+    DevBuf stage;
+    if (!on_device) LB_TRY(stage.ensure(std::min(rows, chunk_rows) * c->p.n * 8));
+    for (uint64_t r0 = 0; r0 < rows; r0 += chunk_rows) {
+        const uint64_t m = std::min(chunk_rows, rows - r0);
+        const u64* src = A + r0 * c->p.n;
+        if (!on_device) {
+            LB_CUDA(cudaMemcpyAsync(stage.p, src, m * c->p.n * 8, cudaMemcpyHostToDevice, c->stream));
+            src = stage.as<u64>();
+        }
+        if (c->ks_elem == 2)
+            pack_ksk_kernel<uint16_t><<<nblk(m * c->npad, 256), 256, 0, c->stream>>>(
+                src, c->kskA.as<uint16_t>() + r0 * c->npad, c->p.n, c->npad, m);
+        else
+            pack_ksk_kernel<u32><<<nblk(m * c->npad, 256), 256, 0, c->stream>>>(src, c->kskA.as<u32>() + r0 * c->npad,
+                                                                               c->p.n, c->npad, m);
+        c->launches++;
+    }
+    {
+        DevBuf sb;
+        const u64* src = B;
+        if (!on_device) {
+            LB_TRY(sb.ensure(rows * 8));
+            LB_CUDA(cudaMemcpyAsync(sb.p, B, rows * 8, cudaMemcpyHostToDevice, c->stream));
+            src = sb.as<u64>();
+        }
+        narrow_u64_u32_kernel<<<nblk(rows, 256), 256, 0, c->stream>>>(src, c->kskB.as<u32>(), rows);
+        c->launches++;
+        LB_CUDA(cudaStreamSynchronize(c->stream));
+        sb.release();
+    }
+    stage.release();
+    c->have_ksk = true;
+    return 0;
+}
+
+int luxb200_synchronize(luxb200_ctx* c) {
+    if (!c) return lb_fail(LUXB200_ERR_INVALID_ARG, "null argument");
+    LB_TRY(lb_set_device(c->device));
+    LB_CUDA(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+}  // extern "C"
+
+#include "api_ops.inc"

@@ -1,0 +1,84 @@
+// api_common.h — host-side context objects shared by the C-ABI translation units.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/luxb200.h"
+#include "br_common.cuh"
+#include "host_math.h"
+
+extern thread_local std::string g_last_error;
+int lb_fail(int code, const char* fmt, ...);
+
+#define LB_CUDA(expr)                                                                                  \
+    do {                                                                                               \
+        cudaError_t e_ = (expr);                                                                       \
+        if (e_ != cudaSuccess)                                                                         \
+            return lb_fail(e_ == cudaErrorNoDevice || e_ == cudaErrorInsufficientDriver ? LUXB200_ERR_NO_DEVICE \
+                                                                                        : LUXB200_ERR_CUDA,    \
+                           "%s failed: %s (%s:%d)", #expr, cudaGetErrorString(e_), __FILE__, __LINE__); \
+    } while (0)
+#define LB_TRY(expr)            \
+    do {                        \
+        int r_ = (expr);        \
+        if (r_ != 0) return r_; \
+    } while (0)
+
+// grow-only device buffer
+struct DevBuf {
+    void* p = nullptr;
+    size_t cap = 0;
+    int ensure(size_t bytes) {
+        if (bytes <= cap) return 0;
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+        cudaError_t e = cudaMalloc(&p, bytes);
+        if (e != cudaSuccess) return lb_fail(LUXB200_ERR_ALLOC, "cudaMalloc(%zu) failed: %s", bytes, cudaGetErrorString(e));
+        cap = bytes;
+        return 0;
+    }
+    void release() {
+        if (p) cudaFree(p);
+        p = nullptr;
+        cap = 0;
+    }
+    template <typename T>
+    T* as() { return reinterpret_cast<T*>(p); }
+};
+
+// u32 NTT tables of one modulus (device) + the uniform constants
+struct Ntt32Tables {
+    uint32_t N = 0, logN = 0, logH = 0;
+    uint64_t Q = 0, psi = 0;
+    NttConsts C;
+    DevBuf twB, twiB, twfull, twifull;
+    int build(uint32_t N, uint64_t Q, uint64_t psi);
+    void release() { twB.release(); twiB.release(); twfull.release(); twifull.release(); }
+};
+
+struct luxb200_ctx {
+    luxb200_params p;
+    int device = 0;
+    uint32_t digitsG = 0, digitsKS = 0, digitsR = 0, rows = 0, logN = 0;
+    uint32_t npad = 0;       // padded KSK row length
+    uint32_t ks_elem = 0;    // bytes per KSK element (2 or 4)
+    uint32_t red_s = 0, red_mu = 0;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    Ntt32Tables ntt;
+    DevBuf bsk, mono, kskA, kskB, automap;
+    bool have_bsk = false, have_ksk = false;
+    // work buffers
+    DevBuf in0, in1, in2, in3, wa, wb, lut, ext, oa, ob, o64a, o64b, sched, tmpa, tmpb, tmpc, tmpd;
+    uint64_t launches = 0;
+    float t_prep = 0, t_br = 0, t_ks = 0, t_total = 0;
+    uint32_t last_launches = 0;
+};
+
+int lb_set_device(int device);

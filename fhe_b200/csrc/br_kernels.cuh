@@ -1,0 +1,233 @@
+// br_kernels.cuh — fused blind rotation (RingGSWAccumulator*::EvalAcc) + test-vector prologue
+// (BootstrapGateCore / BootstrapFuncCore, binfhe-base-scheme.cpp:525-626) + extraction epilogue
+// (Transpose, INTT, b = acc1[0] + offset; binfhe-base-scheme.cpp:111-121, :634-639).
+#pragma once
+#include "br_common.cuh"
+
+enum { M_AP = 1, M_GINX = 2, M_LMKCDEY = 3 };
+
+template <int LOGN, int LOGH, int ROWS, int CTS>
+struct BrSmem {
+    using W = WNtt<LOGN, LOGH>;
+    uint2 twB[W::NB * 32];
+    uint2 twiB[W::NB * 32];
+    u32 scratch[2 * CTS][W::N];        // per-warp transpose scratch
+    uint4 exch[CTS][ROWS][W::N / 4];   // NTT'd digit polynomials, sigma order, shared by the warp pair
+};
+
+// ---- digit pipeline: INTT -> decompose -> NTT -> publish (rows 2k+c) -------------------------------------
+template <int LOGN, int LOGH, int ROWS>
+__device__ __forceinline__ void digits_from_acc(const u32 (&acc)[(1 << LOGN) / 32], u32 (&dg)[ROWS / 2][(1 << LOGN) / 32],
+                                                const BrParams& P, u32* scratch, const uint2* twB, const uint2* twiB,
+                                                uint4* exch /* [ROWS][N/4] */, int c, int lane) {
+    using W         = WNtt<LOGN, LOGH>;
+    constexpr int E = W::E;
+    u32 x[E];
+#pragma unroll
+    for (int r = 0; r < E; ++r) x[r] = acc[r];
+    W::inverse(x, P.C, scratch, twiB, P.twifull, lane);
+#pragma unroll
+    for (int r = 0; r < E; ++r) {
+        u32 d[ROWS / 2];
+        decompose_coeff<ROWS / 2>(x[r], P.C.Q, P.qhalf, (int)P.gbits, d);
+#pragma unroll
+        for (int k = 0; k < ROWS / 2; ++k) dg[k][r] = d[k];
+    }
+#pragma unroll
+    for (int k = 0; k < ROWS / 2; ++k) {
+        W::template forward<1>(dg[k], P.C, scratch, twB, P.twfull, lane);
+        uint4* dst = exch + (2 * k + c) * (W::N / 4);
+#pragma unroll
+        for (int v = 0; v < E / 4; ++v)
+            dst[v * 32 + lane] = make_uint4(dg[k][4 * v], dg[k][4 * v + 1], dg[k][4 * v + 2], dg[k][4 * v + 3]);
+    }
+}
+
+__device__ __forceinline__ u32 comp4(const uint4& v, int e) {
+    return e == 0 ? v.x : e == 1 ? v.y : e == 2 ? v.z : v.w;
+}
+
+// ---- GINX accumulator update (rgsw-acc-cggi.cpp:132-150) -----------------------------------------------
+// acc[c] += (sum_row dct[row] * ek1[row][c]) * mono + (sum_row dct[row] * ek2[row][c]) * monoNeg
+template <int LOGN, int ROWS>
+__device__ __forceinline__ void mac_ginx(u32 (&acc)[(1 << LOGN) / 32], const u32 (&dg)[ROWS / 2][(1 << LOGN) / 32],
+                                         const uint4* exch, const BrParams& P, const u32* ek1, const u32* ek2,
+                                         const u32* mp, const u32* mn, int c, int lane) {
+    constexpr int N = 1 << LOGN, E = N / 32;
+    const u32 Q = P.C.Q, Q2 = P.C.Q2;
+#pragma unroll
+    for (int v = 0; v < E / 4; ++v) {
+        uint4 k1[ROWS], k2[ROWS], dx[ROWS / 2];
+#pragma unroll
+        for (int row = 0; row < ROWS; ++row) {
+            k1[row] = __ldg(reinterpret_cast<const uint4*>(ek1 + (size_t)(row * 2 + c) * N) + v * 32 + lane);
+            k2[row] = __ldg(reinterpret_cast<const uint4*>(ek2 + (size_t)(row * 2 + c) * N) + v * 32 + lane);
+        }
+        const uint4 m1 = __ldg(reinterpret_cast<const uint4*>(mp) + v * 32 + lane);
+        const uint4 m2 = __ldg(reinterpret_cast<const uint4*>(mn) + v * 32 + lane);
+#pragma unroll
+        for (int k = 0; k < ROWS / 2; ++k) dx[k] = exch[(2 * k + (1 - c)) * (N / 4) + v * 32 + lane];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            u64 s1 = 0, s2 = 0;
+#pragma unroll
+            for (int row = 0; row < ROWS; ++row) {
+                const u32 d = ((row & 1) == c) ? dg[row >> 1][4 * v + e] : comp4(dx[row >> 1], e);
+                s1          = mad_wide(d, comp4(k1[row], e), s1);
+                s2          = mad_wide(d, comp4(k2[row], e), s2);
+            }
+            const u32 r1 = reduce64(s1, P.red_s, P.red_mu, Q);
+            const u32 r2 = reduce64(s2, P.red_s, P.red_mu, Q);
+            u64 t        = mad_wide(r1, comp4(m1, e), (u64)acc[4 * v + e]);
+            t            = mad_wide(r2, comp4(m2, e), t);
+            acc[4 * v + e] = csub(reduce64(t, P.red_s, P.red_mu, Q), Q2);
+        }
+    }
+}
+
+// ---- AP / LMKCDEY accumulator update: acc[c] = sum_row dct[row] * ek[row][c]  (replace) ---------------
+template <int LOGN, int ROWS>
+__device__ __forceinline__ void mac_replace(u32 (&acc)[(1 << LOGN) / 32], const u32 (&dg)[ROWS / 2][(1 << LOGN) / 32],
+                                            const uint4* exch, const BrParams& P, const u32* ek, int c, int lane) {
+    constexpr int N = 1 << LOGN, E = N / 32;
+    const u32 Q = P.C.Q, Q2 = P.C.Q2;
+#pragma unroll
+    for (int v = 0; v < E / 4; ++v) {
+        uint4 k1[ROWS], dx[ROWS / 2];
+#pragma unroll
+        for (int row = 0; row < ROWS; ++row)
+            k1[row] = __ldg(reinterpret_cast<const uint4*>(ek + (size_t)(row * 2 + c) * N) + v * 32 + lane);
+#pragma unroll
+        for (int k = 0; k < ROWS / 2; ++k) dx[k] = exch[(2 * k + (1 - c)) * (N / 4) + v * 32 + lane];
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            u64 s1 = 0;
+#pragma unroll
+            for (int row = 0; row < ROWS; ++row) {
+                const u32 d = ((row & 1) == c) ? dg[row >> 1][4 * v + e] : comp4(dx[row >> 1], e);
+                s1          = mad_wide(d, comp4(k1[row], e), s1);
+            }
+            acc[4 * v + e] = csub(reduce64(s1, P.red_s, P.red_mu, Q), Q2);
+        }
+    }
+}
+
+// ---- prologue: test vector -> acc = (0, NTT(m)) --------------------------------------------------------
+template <int LOGN, int LOGH>
+__device__ __forceinline__ void prologue(u32 (&acc)[(1 << LOGN) / 32], const BrParams& P, u32 ct, u32* scratch,
+                                         const uint2* twB, int c, int lane) {
+    using W         = WNtt<LOGN, LOGH>;
+    constexpr int E = W::E;
+    if (c == 0) {
+#pragma unroll
+        for (int r = 0; r < E; ++r) acc[r] = 0;
+        return;
+    }
+    const u32 b = P.b[ct], half = P.ctmod >> 1;
+#pragma unroll
+    for (int r = 0; r < E; ++r) {
+        const u32 j = lane + 32 * r;
+        u32 val     = 0;
+        if (j % P.factor == 0) {
+            const u32 jj = j / P.factor;
+            if (jj < half) val = P.lut[(b + P.ctmod - jj) % P.ctmod];
+        }
+        acc[r] = val;
+    }
+    W::template forward<1>(acc, P.C, scratch, twB, P.twfull, lane);
+}
+
+// ---- epilogue: a' = Transpose(acc0) in coefficient form, b = coeff0(acc1) + b_add -----------------------
+template <int LOGN, int LOGH>
+__device__ __forceinline__ void epilogue(u32 (&acc)[(1 << LOGN) / 32], const BrParams& P, u32 ct, u32* scratch,
+                                         const uint2* twiB, int c, int lane) {
+    using W         = WNtt<LOGN, LOGH>;
+    constexpr int N = W::N, E = W::E;
+    const u32 Q     = P.C.Q;
+    u32* out        = P.ext + (size_t)ct * (N + 1);
+    if (c == 0) {
+        // INTT(Transpose(x)) == coefficient automorphism X -> X^-1 of INTT(x): a'[0] = a[0], a'[N-j] = -a[j]
+        W::inverse(acc, P.C, scratch, twiB, P.twifull, lane);
+#pragma unroll
+        for (int r = 0; r < E; ++r) {
+            const u32 j = lane + 32 * r;
+            const u32 v = acc[r];
+            if (j == 0) out[0] = v;
+            else out[N - j] = v ? Q - v : 0;
+        }
+    } else {
+        // coefficient 0 of INTT(x) is N^-1 * sum_p x[p]
+        u64 s = 0;
+#pragma unroll
+        for (int r = 0; r < E; ++r) s += acc[r];
+#pragma unroll
+        for (int o = 16; o >= 1; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+        if (lane == 0) {
+            u32 sm = (u32)(s % Q);
+            u32 v  = csub(shoup_mul(sm, P.C.ninv, P.C.ninv_s, Q), Q);
+            out[N] = csub(v + P.b_add, Q);
+        }
+    }
+}
+
+// ---- GINX kernel (RingGSWAccumulatorCGGI::EvalAcc, rgsw-acc-cggi.cpp:59-68) -----------------------------
+template <int LOGN, int LOGH, int ROWS, int CTS>
+__global__ void __launch_bounds__(64 * CTS, (LOGN <= 10 && ROWS <= 4) ? 3 : 1)
+br_ginx_kernel(const __grid_constant__ BrParams P) {
+    using W         = WNtt<LOGN, LOGH>;
+    using S         = BrSmem<LOGN, LOGH, ROWS, CTS>;
+    constexpr int N = W::N, E = W::E;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    S& sm = *reinterpret_cast<S*>(smem_raw);
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int slot = warp >> 1, c = warp & 1;
+    for (int i = threadIdx.x; i < W::NB * 32; i += blockDim.x) {
+        sm.twB[i]  = P.twB[i];
+        sm.twiB[i] = P.twiB[i];
+    }
+    __syncthreads();
+    const u32 ct = blockIdx.x * CTS + slot;
+    if (ct >= P.count) return;  // whole warp pair exits together; only pair barriers are used below
+
+    u32* scratch = sm.scratch[warp];
+    uint4* exch  = &sm.exch[slot][0][0];
+    u32 acc[E];
+    if (P.mode == 0) {
+        prologue<LOGN, LOGH>(acc, P, ct, scratch, sm.twB, c, lane);
+    } else {
+        const uint4* src = reinterpret_cast<const uint4*>(P.acc_io + ((size_t)ct * 2 + c) * N);
+#pragma unroll
+        for (int v = 0; v < E / 4; ++v) {
+            uint4 t        = src[v * 32 + lane];
+            acc[4 * v]     = t.x;
+            acc[4 * v + 1] = t.y;
+            acc[4 * v + 2] = t.z;
+            acc[4 * v + 3] = t.w;
+        }
+    }
+    const u32* arow     = P.a + (size_t)ct * P.n;
+    const size_t kblock = (size_t)ROWS * 2 * N;
+    for (u32 i = 0; i < P.n; ++i) {
+        const u32 ai = arow[i];
+        const u32 ap = ((P.ctmod - ai) % P.ctmod) * P.amul;  // (-a_i mod q) * (2N/q)
+        if (ap == 0) continue;                              // X^0 - 1 = 0: the step adds zero
+        u32 dg[ROWS / 2][E];
+        digits_from_acc<LOGN, LOGH, ROWS>(acc, dg, P, scratch, sm.twB, sm.twiB, exch, c, lane);
+        pair_barrier(1 + slot);
+        const u32* ek1 = P.bsk + (size_t)(2 * i) * kblock;
+        const u32* mp  = P.mono + (size_t)ap * N;
+        const u32* mn  = P.mono + (size_t)(2 * N - ap) * N;
+        mac_ginx<LOGN, ROWS>(acc, dg, exch, P, ek1, ek1 + kblock, mp, mn, c, lane);
+        pair_barrier(1 + slot);
+    }
+    if (P.mode == 0) {
+        epilogue<LOGN, LOGH>(acc, P, ct, scratch, sm.twiB, c, lane);
+    } else {
+        uint4* dst = reinterpret_cast<uint4*>(P.acc_io + ((size_t)ct * 2 + c) * N);
+#pragma unroll
+        for (int v = 0; v < E / 4; ++v)
+            dst[v * 32 + lane] = make_uint4(csub(acc[4 * v], P.C.Q), csub(acc[4 * v + 1], P.C.Q),
+                                            csub(acc[4 * v + 2], P.C.Q), csub(acc[4 * v + 3], P.C.Q));
+    }
+}

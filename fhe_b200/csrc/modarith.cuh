@@ -1,0 +1,61 @@
+// modarith.cuh — 32-bit lazy modular arithmetic for sm_100a (Q < 2^30).
+//
+// Every reference operation on this path (ModMulFastConst ubintnat.h:1464-1469, ModMulFast Barrett
+// :1348-1361, ModAddFast/ModSubFast) returns the canonical residue in [0,Q); any exact modular algorithm
+// therefore reproduces the reference bit for bit as long as the value finally stored is canonical.
+// Inside kernels values are kept "lazy" in [0, k*Q) with k tracked at compile time.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+typedef uint32_t u32;
+typedef uint64_t u64;
+typedef int32_t i32;
+
+// Shoup/Harvey multiplication by a constant w with ws = floor(w * 2^32 / Q):
+// valid for ANY x < 2^32, result in [0, 2Q).  1 IMAD.HI + 2 IMAD.
+__device__ __forceinline__ u32 shoup_mul(u32 x, u32 w, u32 ws, u32 Q) {
+    u32 q = __umulhi(x, ws);
+    return x * w - q * Q;
+}
+// x < 2^32  ->  [0, 2Q)   (mu32 = floor(2^32 / Q))
+__device__ __forceinline__ u32 reduce_2q(u32 x, u32 mu32, u32 Q) {
+    u32 q = __umulhi(x, mu32);
+    return x - q * Q;
+}
+// conditional subtract: x in [0, 2m) -> [0, m)
+__device__ __forceinline__ u32 csub(u32 x, u32 m) {
+    return min(x, x - m);
+}
+// 64-bit -> [0, 4Q): x < 2^(s+32), mu = floor(2^(s+32) / Q) < 2^32, s <= bits(Q)-1
+__device__ __forceinline__ u32 reduce64(u64 x, u32 s, u32 mu, u32 Q) {
+    u32 xh = (u32)(x >> s);
+    u32 q  = __umulhi(xh, mu);
+    return (u32)x - q * Q;
+}
+__device__ __forceinline__ u64 mad_wide(u32 a, u32 b, u64 c) {
+    return (u64)a * b + c;
+}
+__device__ __forceinline__ i32 sext(i32 v, int bits) {
+    i32 r;
+    asm("bfe.s32 %0, %1, 0, %2;" : "=r"(r) : "r"(v), "r"(bits));
+    return r;
+}
+
+// RoundqQ (lwe-pke.cpp:41-46): floor(0.5 + double(v) * double(q) / double(Q)) mod q, IEEE double,
+// round-to-nearest, no FMA contraction — the same operation sequence as the x86-64 reference build.
+__device__ __forceinline__ u64 round_qQ(u64 v, u64 q, u64 Q) {
+    double prod = __dmul_rn((double)v, (double)q);
+    double quo  = __ddiv_rn(prod, (double)Q);
+    double r    = floor(__dadd_rn(0.5, quo));
+    return (u64)r % q;
+}
+
+// 64-bit modular helpers for the u64 NTT path (Q < 2^62)
+__device__ __forceinline__ u64 shoup_mul64(u64 x, u64 w, u64 ws, u64 Q) {
+    u64 q = __umul64hi(x, ws);
+    return x * w - q * Q;  // [0, 2Q)
+}
+__device__ __forceinline__ u64 csub64(u64 x, u64 m) {
+    return x >= m ? x - m : x;
+}

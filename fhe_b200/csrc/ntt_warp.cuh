@@ -1,0 +1,209 @@
+// ntt_warp.cuh — one-warp-per-polynomial negacyclic NTT/INTT for N = 2^LOGN (256 <= N <= 2048), u32 lazy.
+//
+// Computes exactly what NumberTheoreticTransformNat::ForwardTransformToBitReverseInPlace
+// (transformnat-impl.h:302-373) and ::InverseTransformFromBitReverseInPlace (:511-624) compute:
+// Cooley-Tukey, natural order in -> bit-reversed out with twiddle Table[brv(i)] = psi^i (:777-831), and
+// Gentleman-Sande bit-reversed in -> natural out with the N^-1 scaling folded into the last stage.
+//
+// B200 mapping: each lane keeps E = N/32 coefficients in registers.
+//   layout A: reg r of lane l holds index j = l + 32 r   (strides >= 32 are in-thread)
+//   layout B: reg r of lane l holds index p = E l + r    (strides <  E  are in-thread)
+// A 2^LOGN transform is: phase A (in-register, twiddles uniform across the warp -> read from the kernel
+// parameter constant bank), [shuffle stages when E < 32], ONE swizzled shared-memory transpose, phase B
+// (in-register, per-lane twiddles from a lane-major shared-memory table).  So a whole NTT costs one
+// shared-memory round trip of the data instead of log2(N).
+#pragma once
+#include "modarith.cuh"
+
+// uniform (warp-wide) constants, passed by value as a __grid_constant__ kernel parameter
+struct NttConsts {
+    uint2 twA[64];   // forward  table entries 1..E-1 : (w, floor(w 2^32/Q))
+    uint2 twiA[64];  // inverse  table entries 1..E-1
+    u32 Q, Q2, mu32;
+    u32 ninv, ninv_s;      // N^-1 and its Shoup companion
+    u32 w1ninv, w1ninv_s;  // TableI[1] * N^-1 (transformnat-impl.h:537-538)
+    u32 pad;
+};
+
+template <int LOGN, int LOGH>
+struct WNtt {
+    static constexpr int N    = 1 << LOGN;
+    static constexpr int E    = N / 32;
+    static constexpr int LOGE = LOGN - 5;
+    static constexpr int TB   = (E / 2 < 16) ? E / 2 : 16;  // largest in-thread stride of phase B
+    static constexpr int H    = 1 << LOGH;                  // Q < 2^(32-LOGH): values < H*Q fit in 32 bits
+
+    __host__ __device__ static constexpr int offB(int t) {  // first entry of stage t in the lane-major table
+        int o = 0;
+        for (int tt = TB; tt > t; tt >>= 1) o += E / (2 * tt);
+        return o;
+    }
+    static constexpr int NB = offB(1) + E / 2;  // phase-B twiddles per lane
+
+    // bank-conflict-free swizzle for the A<->B transpose
+    __device__ static __forceinline__ u32 phys(u32 j) {
+        u32 f = (E >= 32) ? ((j >> LOGE) & 31u) : ((j >> 5) & 31u);
+        return j ^ f;
+    }
+    __device__ static __forceinline__ void store_A(u32* sm, const u32 (&x)[E], int lane) {
+#pragma unroll
+        for (int r = 0; r < E; ++r) sm[phys(lane + 32 * r)] = x[r];
+    }
+    __device__ static __forceinline__ void load_A(const u32* sm, u32 (&x)[E], int lane) {
+#pragma unroll
+        for (int r = 0; r < E; ++r) x[r] = sm[phys(lane + 32 * r)];
+    }
+    __device__ static __forceinline__ void store_B(u32* sm, const u32 (&x)[E], int lane) {
+#pragma unroll
+        for (int r = 0; r < E; ++r) sm[phys(E * lane + r)] = x[r];
+    }
+    __device__ static __forceinline__ void load_B(const u32* sm, u32 (&x)[E], int lane) {
+#pragma unroll
+        for (int r = 0; r < E; ++r) x[r] = sm[phys(E * lane + r)];
+    }
+
+    __device__ static __forceinline__ void ct(u32& a, u32& b, u32 w, u32 ws, u32 Q, u32 Q2) {
+        u32 u = shoup_mul(b, w, ws, Q);
+        b     = a - u + Q2;
+        a     = a + u;
+    }
+
+    // ---- forward: layout A in (values < B0*Q), layout B out in [0, 2Q) ------------------------------------
+    // sm: N u32 of scratch private to this warp; twB: lane-major phase-B table (shared memory);
+    // twfull: full (w, ws) table [N] in global memory, used only by the shuffle stages (E < 32).
+    template <int B0>
+    __device__ static __forceinline__ void forward(u32 (&x)[E], const NttConsts& C, u32* sm, const uint2* twB,
+                                                   const uint2* __restrict__ twfull, int lane) {
+        const u32 Q = C.Q, Q2 = C.Q2;
+        int bound = B0;
+#pragma unroll
+        for (int tr = E / 2; tr >= 1; tr >>= 1) {
+            if (bound + 2 > H) {
+#pragma unroll
+                for (int r = 0; r < E; ++r) x[r] = reduce_2q(x[r], C.mu32, Q);
+                bound = 2;
+            }
+            const int m = E / (2 * tr);
+#pragma unroll
+            for (int i = 0; i < m; ++i) {
+                const uint2 w = C.twA[m + i];
+#pragma unroll
+                for (int r = 2 * i * tr; r < 2 * i * tr + tr; ++r) ct(x[r], x[r + tr], w.x, w.y, Q, Q2);
+            }
+            bound += 2;
+        }
+        if (E < 32) {
+#pragma unroll
+            for (int t = 16; t >= E; t >>= 1) {
+                if (bound + 2 > H) {
+#pragma unroll
+                    for (int r = 0; r < E; ++r) x[r] = reduce_2q(x[r], C.mu32, Q);
+                    bound = 2;
+                }
+                const bool hi = lane & t;
+#pragma unroll
+                for (int r = 0; r < E; ++r) {
+                    const uint2 w = twfull[N / (2 * t) + (32 * r + lane) / (2 * t)];
+                    u32 u         = shoup_mul(x[r], w.x, w.y, Q);
+                    u32 v         = __shfl_xor_sync(0xffffffffu, hi ? u : x[r], t);
+                    x[r]          = hi ? (v - u + Q2) : (x[r] + v);
+                }
+                bound += 2;
+            }
+        }
+        __syncwarp();
+        store_A(sm, x, lane);
+        __syncwarp();
+        load_B(sm, x, lane);
+#pragma unroll
+        for (int t = TB; t >= 1; t >>= 1) {
+            if (bound + 2 > H) {
+#pragma unroll
+                for (int r = 0; r < E; ++r) x[r] = reduce_2q(x[r], C.mu32, Q);
+                bound = 2;
+            }
+            const int g = E / (2 * t);
+#pragma unroll
+            for (int i = 0; i < g; ++i) {
+                const uint2 w = twB[(offB(t) + i) * 32 + lane];
+#pragma unroll
+                for (int r = 2 * i * t; r < 2 * i * t + t; ++r) ct(x[r], x[r + t], w.x, w.y, Q, Q2);
+            }
+            bound += 2;
+        }
+        if (bound > 2) {
+#pragma unroll
+            for (int r = 0; r < E; ++r) x[r] = reduce_2q(x[r], C.mu32, Q);
+        }
+    }
+
+    // ---- inverse: layout B in (values in [0, 2Q)), layout A out, canonical [0, Q) --------------------------
+    __device__ static __forceinline__ void gs(u32& a, u32& b, u32 w, u32 ws, u32 Q, u32 BQ, bool red, u32 mu32) {
+        u32 d = a - b + BQ;
+        a     = a + b;
+        if (red) a = reduce_2q(a, mu32, Q);
+        b = shoup_mul(d, w, ws, Q);
+    }
+    __device__ static __forceinline__ void inverse(u32 (&x)[E], const NttConsts& C, u32* sm, const uint2* twiB,
+                                                   const uint2* __restrict__ twifull, int lane) {
+        const u32 Q = C.Q;
+        int bound   = 2;  // 2*bound <= H holds on entry to every stage
+#pragma unroll
+        for (int t = 1; t <= TB; t <<= 1) {
+            const bool red = 4 * bound > H;
+            const int g    = E / (2 * t);
+#pragma unroll
+            for (int i = 0; i < g; ++i) {
+                const uint2 w = twiB[(offB(t) + i) * 32 + lane];
+#pragma unroll
+                for (int r = 2 * i * t; r < 2 * i * t + t; ++r)
+                    gs(x[r], x[r + t], w.x, w.y, Q, (u32)bound * Q, red, C.mu32);
+            }
+            bound = red ? 2 : 2 * bound;
+        }
+        __syncwarp();
+        store_B(sm, x, lane);
+        __syncwarp();
+        load_A(sm, x, lane);
+        if (E < 32) {
+#pragma unroll
+            for (int t = E; t <= 16; t <<= 1) {
+                const bool red = 4 * bound > H;
+                const bool hi  = lane & t;
+#pragma unroll
+                for (int r = 0; r < E; ++r) {
+                    const uint2 w = twifull[N / (2 * t) + (32 * r + lane) / (2 * t)];
+                    u32 v         = __shfl_xor_sync(0xffffffffu, x[r], t);
+                    u32 s         = x[r] + v;
+                    if (red) s = reduce_2q(s, C.mu32, Q);
+                    u32 d = shoup_mul(v - x[r] + (u32)bound * Q, w.x, w.y, Q);
+                    x[r]  = hi ? d : s;
+                }
+                bound = red ? 2 : 2 * bound;
+            }
+        }
+#pragma unroll
+        for (int tr = 1; tr < E / 2; tr <<= 1) {
+            const bool red = 4 * bound > H;
+            const int m    = E / (2 * tr);
+#pragma unroll
+            for (int i = 0; i < m; ++i) {
+                const uint2 w = C.twiA[m + i];
+#pragma unroll
+                for (int r = 2 * i * tr; r < 2 * i * tr + tr; ++r)
+                    gs(x[r], x[r + tr], w.x, w.y, Q, (u32)bound * Q, red, C.mu32);
+            }
+            bound = red ? 2 : 2 * bound;
+        }
+        // last stage (t = N/2) with N^-1 folded in; outputs canonical
+        {
+            const u32 BQ = (u32)bound * Q;
+#pragma unroll
+            for (int r = 0; r < E / 2; ++r) {
+                u32 a = x[r], b = x[r + E / 2];
+                x[r]         = csub(shoup_mul(a + b, C.ninv, C.ninv_s, Q), Q);
+                x[r + E / 2] = csub(shoup_mul(a - b + BQ, C.w1ninv, C.w1ninv_s, Q), Q);
+            }
+        }
+    }
+};

@@ -1,0 +1,145 @@
+/* luxb200.h — C ABI of libluxb200.so: B200-native (sm_100a) batched TFHE/FHEW bootstrapping + bit-reverse NTT.
+ *
+ * Drop-in boundary for luxcpp/fhe's batched hot path.  Every entry point replaces a reference interface
+ * (file:line relative to the reference tree):
+ *
+ *   luxb200_evalbingate_batch       lux::fhe::EvalBinGateBatch            src/binfhe/include/batch/binfhe-batch.h:100-111
+ *                                   (= OMP loop over BinFHEContext::EvalBinGate, src/binfhe/lib/batch/batch.cpp:176-210;
+ *                                   BinFHEScheme::EvalBinGate src/binfhe/lib/binfhe-base-scheme.cpp:76-126)
+ *   luxb200_evalbingate_multi_batch BinFHEScheme::EvalBinGate(vector)     src/binfhe/lib/binfhe-base-scheme.cpp:129-187
+ *                                   and lux::fhe::EvalCMUXBatch            binfhe-batch.h:113-125
+ *   luxb200_bootstrap_batch         lux::fhe::BootstrapBatch               binfhe-batch.h:48-58 (spec: BinFHEScheme::Bootstrap,
+ *                                                                          binfhe-base-scheme.cpp:190-220)
+ *   luxb200_evalfunc_batch          lux::fhe::EvalFuncBatch                binfhe-batch.h:60-75 (BinFHEScheme::EvalFunc,
+ *                                                                          binfhe-base-scheme.cpp:241-332)
+ *   luxb200_blind_rotate_batch      backend::Backend::BlindRotateBatch     src/binfhe/include/backend/backend.h:177-183
+ *                                   (RingGSWAccumulator::EvalAcc, src/binfhe/include/rgsw-acc.h:73-76)
+ *   luxb200_keyswitch_batch         backend::Backend::KeySwitchBatch       backend.h:196-202 (LWEEncryptionScheme::KeySwitch,
+ *                                                                          src/binfhe/lib/lwe-pke.cpp:348-372)
+ *   luxb200_modswitch_batch         backend::Backend::ModSwitchBatch       backend.h:204-211 (lwe-pke.cpp:254-261)
+ *   luxb200_ntt_batch               PolyImpl::SwitchFormat                 src/core/include/lattice/hal/default/poly-impl.h:420-440
+ *                                   (NumberTheoreticTransformNat, src/core/include/math/hal/intnat/transformnat-impl.h:302-373,511-624)
+ *   luxb200_dcrt_ntt_batch          DCRTPolyImpl::SwitchFormat             src/core/include/lattice/hal/default/dcrtpoly-impl.h:1953-1959
+ *   luxb200_load_bsk / _ksk         backend::Backend::PackBootstrappingKey backend.h:223-233 (flat layouts below)
+ *   luxb200_ctx_create              BinFHEContext::GenerateBinFHEContext   src/binfhe/lib/binfhecontext.cpp:109-187 (parameters only)
+ *
+ * Conventions (same as the reference's C ABI, include/lux/fhe/c_api.h:47-70): every call returns 0 on
+ * success or a negative LUXB200_ERR_* code; no exception crosses the boundary; luxb200_last_error() gives
+ * the message of the calling thread's last failure.  Host buffers are caller-owned; ciphertext data uses
+ * the reference's NativeVector element type (uint64_t, one residue per element).  There is NO CPU fallback:
+ * without a CUDA device every compute call fails with LUXB200_ERR_NO_DEVICE.
+ *
+ * Canonical flat key layouts (EVALUATION format, the reference's own coefficient order):
+ *   BSK  GINX    [n][2][rows][2][N]              ([i][0] = (*ek)[0][0][i], [i][1] = (*ek)[0][1][i]; rgsw-acc-cggi.cpp:39-57)
+ *        AP      [n][baseR][digitsR][rows][2][N] ((*ek)[i][j][k]; j = 0 unused; rgsw-acc-dm.cpp:39-60)
+ *        LMKCDEY [n][rows][2][N] then [numAutoKeys+1][digitsG-1][2][N]  ((*ek)[0][0][i]; (*ek)[0][1][t]; rgsw-acc-lmkcdey.cpp:39-68)
+ *        rows = 2*(digitsG-1)
+ *   KSK  A [N][baseKS][digitsKS][n], B [N][baseKS][digitsKS]   (LWESwitchingKeyImpl, lwe-keyswitchkey.h:49-58)
+ */
+#ifndef LUXB200_H
+#define LUXB200_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define LUXB200_OK 0
+#define LUXB200_ERR_INVALID_ARG (-1)
+#define LUXB200_ERR_NO_DEVICE (-2)
+#define LUXB200_ERR_CUDA (-3)
+#define LUXB200_ERR_UNSUPPORTED (-4)
+#define LUXB200_ERR_NO_KEYS (-5)
+#define LUXB200_ERR_ALLOC (-6)
+
+/* BINFHE_METHOD (binfhe-constants.h:112-117) and BINGATE (:123) values */
+enum { LUXB200_AP = 1, LUXB200_GINX = 2, LUXB200_LMKCDEY = 3 };
+enum { LUXB200_OR, LUXB200_AND, LUXB200_NOR, LUXB200_NAND, LUXB200_XOR, LUXB200_XNOR, LUXB200_MAJORITY,
+       LUXB200_AND3, LUXB200_OR3, LUXB200_AND4, LUXB200_OR4, LUXB200_XOR_FAST, LUXB200_XNOR_FAST, LUXB200_CMUX };
+
+typedef struct luxb200_ctx luxb200_ctx;
+
+typedef struct {
+    uint32_t n, N;            /* LWE dimension, ring dimension */
+    uint64_t q, Q, qKS;       /* LWE modulus, RLWE (NTT) modulus, key-switch modulus */
+    uint32_t baseKS, baseG, baseR, numAutoKeys;
+    uint32_t method;          /* LUXB200_AP / GINX / LMKCDEY */
+    uint32_t reserved;
+    uint64_t psi;             /* primitive 2N-th root of unity mod Q; 0 = compute the minimal one (nbtheory-impl.h:183-231) */
+} luxb200_params;
+
+const char* luxb200_last_error(void);
+int luxb200_version(void);
+int luxb200_device_count(void);
+
+/* ---- number theory used for table generation (host) ------------------------------------------------ */
+uint64_t luxb200_last_prime(uint32_t bits, uint64_t m);      /* LastPrime, nbtheory-impl.h:350-373 */
+uint64_t luxb200_previous_prime(uint64_t q, uint64_t m);     /* PreviousPrime, nbtheory-impl.h:386-393 */
+uint64_t luxb200_root_of_unity(uint64_t m, uint64_t q);      /* RootOfUnity, nbtheory-impl.h:183-231 */
+
+/* ---- context ----------------------------------------------------------------------------------------- */
+int luxb200_ctx_create(const luxb200_params* p, int device, luxb200_ctx** out);
+void luxb200_ctx_destroy(luxb200_ctx* ctx);
+/* out[16]: n N q Q qKS baseKS baseG baseR digitsG numAutoKeys 0 psi digitsKS method digitsR device */
+int luxb200_ctx_info(luxb200_ctx* ctx, uint64_t* out);
+uint64_t luxb200_bsk_len(luxb200_ctx* ctx);   /* elements of the canonical flat BSK */
+uint64_t luxb200_ksk_len(luxb200_ctx* ctx);   /* elements of KSK A (B has ksk_len / n) */
+/* keys in the canonical layout; on_device != 0: the pointers are device pointers on ctx's device
+ * (e.g. the receive buffer of an NCCL broadcast) */
+int luxb200_load_bsk(luxb200_ctx* ctx, const uint64_t* bsk, int on_device);
+int luxb200_load_ksk(luxb200_ctx* ctx, const uint64_t* A, const uint64_t* B, int on_device);
+int luxb200_synchronize(luxb200_ctx* ctx);
+
+/* ---- batched operators, HOST buffers (H2D / D2H inside) ---------------------------------------------- */
+/* a1,a2 [count][n], b1,b2 [count] mod q; out oa [count][n] (or [count][N] mod Q when extended), ob [count] */
+int luxb200_evalbingate_batch(luxb200_ctx* ctx, int gate, const uint64_t* a1, const uint64_t* b1, const uint64_t* a2,
+                              const uint64_t* b2, uint64_t* oa, uint64_t* ob, uint64_t count, int extended);
+/* a [count][k][n], b [count][k]; p = plaintext modulus of the inputs (GetptModulus) */
+int luxb200_evalbingate_multi_batch(luxb200_ctx* ctx, int gate, uint32_t k, const uint64_t* a, const uint64_t* b,
+                                    uint64_t* oa, uint64_t* ob, uint64_t count, uint64_t p);
+int luxb200_bootstrap_batch(luxb200_ctx* ctx, const uint64_t* a, const uint64_t* b, uint64_t* oa, uint64_t* ob,
+                            uint64_t count, uint64_t p, int extended);
+/* lut [lutlen] over Z_ctmod (GenerateLUTviaFunction, binfhecontext.cpp:372-387); beta = BinFHEContext::GetBeta() */
+int luxb200_evalfunc_batch(luxb200_ctx* ctx, const uint64_t* a, const uint64_t* b, const uint64_t* lut,
+                           uint64_t lutlen, uint64_t beta, uint64_t* oa, uint64_t* ob, uint64_t count, uint64_t ctmod);
+/* a [count][n] mod amod; acc [count][2][N] EVALUATION format, in place */
+int luxb200_blind_rotate_batch(luxb200_ctx* ctx, const uint64_t* a, uint64_t amod, uint64_t* acc, uint64_t count);
+/* a [count][N] mod qKS, b [count]  ->  oa [count][n], ob [count] mod qKS */
+int luxb200_keyswitch_batch(luxb200_ctx* ctx, const uint64_t* a, const uint64_t* b, uint64_t* oa, uint64_t* ob,
+                            uint64_t count);
+/* elementwise RoundqQ (lwe-pke.cpp:41-46) over len values */
+int luxb200_modswitch_batch(luxb200_ctx* ctx, uint64_t qto, uint64_t qfrom, const uint64_t* in, uint64_t* out,
+                            uint64_t len);
+
+/* ---- NTT (context-free plan objects) ----------------------------------------------------------------- */
+typedef struct luxb200_ntt_plan luxb200_ntt_plan;
+/* L moduli q[l] with 2N-th roots psi[l] (psi may be NULL: minimal roots are computed). N = 2^k, 256..131072 */
+int luxb200_ntt_plan_create(uint32_t N, uint32_t L, const uint64_t* q, const uint64_t* psi, int device,
+                            luxb200_ntt_plan** out);
+void luxb200_ntt_plan_destroy(luxb200_ntt_plan* plan);
+/* data [count][L][N] uint64 host, in place; inverse = 0: COEFFICIENT->EVALUATION, 1: EVALUATION->COEFFICIENT */
+int luxb200_ntt_batch(luxb200_ntt_plan* plan, uint64_t* data, uint64_t count, int inverse);
+/* device-resident variants: data on the plan's device. elem_bytes 4 (only when every q < 2^30) or 8 */
+int luxb200_ntt_batch_dev(luxb200_ntt_plan* plan, void* data_dev, uint64_t count, int inverse, int elem_bytes);
+int luxb200_ntt_plan_sync(luxb200_ntt_plan* plan);
+float luxb200_ntt_last_ms(luxb200_ntt_plan* plan);   /* CUDA-event time of the last *_dev call's kernels */
+#define luxb200_dcrt_ntt_batch luxb200_ntt_batch     /* DCRTPoly::SwitchFormat = the L > 1 case */
+
+/* ---- device-resident batched gates (inputs already in HBM as uint32) ---------------------------------- */
+/* a1,a2 [count][n] u32, b1,b2 [count] u32 on ctx's device; out oa [count][n] u32, ob [count] u32. Asynchronous on the
+ * context stream; call luxb200_synchronize before reading. */
+int luxb200_evalbingate_batch_dev(luxb200_ctx* ctx, int gate, const uint32_t* a1, const uint32_t* b1,
+                                  const uint32_t* a2, const uint32_t* b2, uint32_t* oa, uint32_t* ob, uint64_t count);
+/* CUDA-event times (ms) of the kernels of the last gate/bootstrap call on this context:
+ * out[0] prep, out[1] blind rotation, out[2] key switch, out[3] total; out[4] = number of kernel launches */
+int luxb200_last_timing(luxb200_ctx* ctx, float* out);
+/* cumulative number of kernels this library launched on the context (for bench.py's gpu_launches) */
+uint64_t luxb200_launch_count(luxb200_ctx* ctx);
+
+/* ---- integer-pipe roofline probe: measured IMAD-class issue rate of this GPU (ops/s) ------------------- */
+int luxb200_intpipe_probe(int device, double* imad_per_s, double* mixed_per_s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
