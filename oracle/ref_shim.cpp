@@ -58,6 +58,21 @@ void* ref_ctx_create(int paramset, int method) {
     }
 }
 
+// custom parameter set: BinFHEContext::GenerateBinFHEContext(const BinFHEContextParams&, method), binfhecontext.cpp:176-187
+void* ref_ctx_create_custom(uint32_t bits, uint32_t cyclOrder, uint32_t n, uint32_t q, uint32_t modKS, uint32_t baseKS,
+                            uint32_t baseG, uint32_t baseR, uint32_t numAutoKeys, int keyDist, int method) {
+    try {
+        auto* h = new RefCtx();
+        BinFHEContextParams p{bits, cyclOrder, n, q, modKS, 3.19, baseKS, baseG, baseR, numAutoKeys,
+                              static_cast<SecretKeyDist>(keyDist)};
+        h->cc.GenerateBinFHEContext(p, static_cast<BINFHE_METHOD>(method));
+        return h;
+    }
+    catch (...) {
+        return nullptr;
+    }
+}
+
 void ref_ctx_destroy(void* hv) {
     delete static_cast<RefCtx*>(hv);
 }

@@ -93,6 +93,7 @@ def ref():
         L = C.CDLL(os.path.join(OUT, "libref_shim.so"))
         _sig(L.ref_ctx_create, VP, [INT, INT])
         _sig(L.ref_ctx_destroy, None, [VP])
+        _sig(L.ref_ctx_create_custom, VP, [U32, U32, U32, U32, U32, U32, U32, U32, U32, INT, INT])
         _sig(L.ref_ctx_params, INT, [VP, VP])
         _sig(L.ref_keygen, INT, [VP])
         _sig(L.ref_get_sk, INT, [VP, VP])
@@ -148,9 +149,13 @@ class Params:
 class RefContext:
     """The reference's BinFHEContext with keys, plus flat dumps of its keys in the canonical layout."""
 
-    def __init__(self, paramset, method):
+    def __init__(self, paramset, method, custom=None):
+        """custom = (bits, cyclOrder, n, q, modKS, baseKS, baseG, baseR, numAutoKeys, keyDist) for a hand-made set."""
         self.L = ref()
-        self.h = self.L.ref_ctx_create(PARAMSET[paramset], METHOD[method])
+        if custom is not None:
+            self.h = self.L.ref_ctx_create_custom(*custom, METHOD[method])
+        else:
+            self.h = self.L.ref_ctx_create(PARAMSET[paramset], METHOD[method])
         assert self.h, "reference rejected the parameter set / method"
         arr = np.zeros(16, np.uint64)
         self.L.ref_ctx_params(self.h, P(arr))
