@@ -1,7 +1,7 @@
 // api.cu — C ABI of libluxb200.so (see include/luxb200.h for the reference interfaces each entry replaces).
 #include "api_common.h"
 #include "aux_kernels.cuh"
-#include "br_kernels.cuh"
+#include "br_sched.cuh"
 #include "ntt_kernels.cuh"
 
 thread_local std::string g_last_error;
@@ -171,6 +171,19 @@ int luxb200_ctx_create(const luxb200_params* p, int device, luxb200_ctx** out) {
         if (!rc && cudaMemcpy(c->automap.p, h.data(), h.size() * 4, cudaMemcpyHostToDevice) != cudaSuccess)
             rc = lb_fail(LUXB200_ERR_CUDA, "automap upload failed");
         if (rc) { luxb200_ctx_destroy(c); return rc; }
+        // logGen (rgsw-cryptoparameters.cpp:115-127)
+        std::vector<i32> lg(M, 0);
+        uint32_t gp = 1;
+        lg[M - gp] = (i32)M;
+        for (uint32_t i = 1; i < N / 2; ++i) {
+            gp = (gp * 5) % M;
+            lg[gp] = (i32)i;
+            lg[M - gp] = -(i32)i;
+        }
+        rc = c->loggen.ensure(M * 4);
+        if (!rc && cudaMemcpy(c->loggen.p, lg.data(), M * 4, cudaMemcpyHostToDevice) != cudaSuccess)
+            rc = lb_fail(LUXB200_ERR_CUDA, "logGen upload failed");
+        if (rc) { luxb200_ctx_destroy(c); return rc; }
     }
     // KSK element type
     c->ks_elem = (p->qKS <= 65536) ? 2 : 4;
@@ -182,7 +195,7 @@ int luxb200_ctx_create(const luxb200_params* p, int device, luxb200_ctx** out) {
 void luxb200_ctx_destroy(luxb200_ctx* c) {
     if (!c) return;
     cudaSetDevice(c->device);
-    DevBuf* bufs[] = {&c->bsk, &c->mono, &c->kskA, &c->kskB, &c->automap, &c->in0, &c->in1, &c->in2, &c->in3, &c->wa,
+    DevBuf* bufs[] = {&c->bsk, &c->mono, &c->kskA, &c->kskB, &c->automap, &c->loggen, &c->in0, &c->in1, &c->in2, &c->in3, &c->wa,
                       &c->wb, &c->lut, &c->ext, &c->oa, &c->ob, &c->o64a, &c->o64b, &c->sched, &c->tmpa, &c->tmpb,
                       &c->tmpc, &c->tmpd};
     for (DevBuf* b : bufs) b->release();

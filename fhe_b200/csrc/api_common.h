@@ -72,7 +72,7 @@ struct luxb200_ctx {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     Ntt32Tables ntt;
-    DevBuf bsk, mono, kskA, kskB, automap;
+    DevBuf bsk, mono, kskA, kskB, automap, loggen;
     bool have_bsk = false, have_ksk = false;
     // work buffers
     DevBuf in0, in1, in2, in3, wa, wb, lut, ext, oa, ob, o64a, o64b, sched, tmpa, tmpb, tmpc, tmpd;

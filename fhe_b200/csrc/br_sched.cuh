@@ -1,0 +1,209 @@
+// br_sched.cuh — AP (RingGSWAccumulatorDM::EvalAcc, rgsw-acc-dm.cpp:62-77) and LMKCDEY
+// (RingGSWAccumulatorLMKCDEY::EvalAcc, rgsw-acc-lmkcdey.cpp:70-158) blind rotation.
+// Both walk a per-ciphertext op list that a small pre-kernel derives from the LWE mask exactly as the
+// reference's loops do; the fused kernel then executes it with the accumulator resident in registers.
+#pragma once
+#include "br_kernels.cuh"
+
+enum : u32 { OP_END = 0u, OP_EXT = 1u << 30, OP_AUTO = 2u << 30, OP_PERM1 = 3u << 30, OP_MASK = 3u << 30 };
+
+// ---- schedules -------------------------------------------------------------------------------------------------
+// AP: for i < n, k < digitsR: a0 = k-th base-baseR digit of (0 - a_i mod q) [u64 arithmetic exactly as
+// NativeInteger::ModSubFast + Mod + /=]; if a0 != 0 -> ext-product with ek[i][a0][k]
+__global__ void sched_ap_kernel(const u32* __restrict__ a, u32* __restrict__ sched, u32 n, u32 stride, u64 q, u32 baseR,
+                                u32 digitsR, u64 count) {
+    const u64 ct = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (ct >= count) return;
+    const u32* ar = a + ct * n;
+    u32* s = sched + ct * stride;
+    u32 pos = 0;
+    for (u32 i = 0; i < n; ++i) {
+        const u64 ai = ar[i];
+        u64 aI = (0 < ai) ? (u64)0 + q - ai : 0;  // ModSubFast(0, a, q), wraps like the reference if a > q
+        for (u32 k = 0; k < digitsR; ++k, aI /= baseR) {
+            const u32 a0 = (u32)(aI % baseR);
+            if (a0) s[pos++] = OP_EXT | ((i * baseR + a0) * digitsR + k);
+        }
+    }
+    s[pos] = OP_END;
+}
+
+// LMKCDEY: one warp per ciphertext; buckets by logGen[(-a_i mod 2N) | 1] (ascending i inside a bucket), then the
+// two sweeps i = N/2-1 .. 1 with automorphisms every numAutoKeys skips (rgsw-acc-lmkcdey.cpp:83-157).
+__global__ void __launch_bounds__(32) sched_lmkcdey_kernel(const u32* __restrict__ a, const i32* __restrict__ logGen,
+                                                           u32* __restrict__ sched, u32 n, u32 stride, u32 N, u32 w) {
+    extern __shared__ i32 sm_s[];
+    const u32 Nh = N / 2, M = 2 * N;
+    i32* first = sm_s;               // [2*Nh + 1] : key + Nh, key M -> slot 2*Nh
+    i32* next  = sm_s + 2 * Nh + 1;  // [n]
+    i32* keyof = next + n;           // [n]
+    const u64 ct = blockIdx.x;
+    const u32* ar = a + ct * n;
+    for (u32 i = threadIdx.x; i < 2 * Nh + 1; i += 32) first[i] = -1;
+    for (u32 i = threadIdx.x; i < n; i += 32) {
+        const u32 ai = ar[i];
+        const u32 aodd = ((ai == 0) ? 0u : (M - ai)) | 1u;
+        const i32 lg = logGen[aodd];
+        keyof[i] = (lg == (i32)M) ? (i32)(2 * Nh) : lg + (i32)Nh;
+    }
+    __syncwarp();
+    if (threadIdx.x != 0) return;
+    for (i32 i = (i32)n - 1; i >= 0; --i) {
+        next[i] = first[keyof[i]];
+        first[keyof[i]] = i;
+    }
+    u32* s = sched + ct * stride;
+    u32 pos = 0, nSkips = 0;
+    s[pos++] = OP_PERM1 | 0u;  // acc[1] <- AutomorphismTransform(2N - 5)
+    for (int pass = 0; pass < 2; ++pass) {
+        for (u32 i = Nh - 1; i > 0; --i) {
+            const i32 slot = pass == 0 ? (i32)Nh - (i32)i : (i32)Nh + (i32)i;
+            if (first[slot] >= 0) {
+                if (nSkips != 0) { s[pos++] = OP_AUTO | nSkips; nSkips = 0; }
+                for (i32 j = first[slot]; j >= 0; j = next[j]) s[pos++] = OP_EXT | (u32)j;
+            }
+            nSkips++;
+            if (nSkips == w || i == 1) { s[pos++] = OP_AUTO | nSkips; nSkips = 0; }
+        }
+        if (pass == 0) {
+            for (i32 j = first[2 * Nh]; j >= 0; j = next[j]) s[pos++] = OP_EXT | (u32)j;  // a_j = -1
+            s[pos++] = OP_AUTO | 0u;                                                        // by 2N - 5
+        } else {
+            for (i32 j = first[Nh]; j >= 0; j = next[j]) s[pos++] = OP_EXT | (u32)j;       // a_j = 5^0
+        }
+    }
+    s[pos] = OP_END;
+}
+
+// ---- EVALUATION-format automorphism of a register-resident polynomial (poly-impl.h:345-356) --------------------
+// map: sigma-ordered source indices; out[p] = in[map[p]]
+template <int LOGN, int LOGH>
+__device__ __forceinline__ void permute_eval(u32 (&x)[(1 << LOGN) / 32], u32* scratch, const u32* __restrict__ map, int lane) {
+    using W = WNtt<LOGN, LOGH>;
+    constexpr int E = W::E;
+    __syncwarp();
+    W::store_B(scratch, x, lane);
+    __syncwarp();
+#pragma unroll
+    for (int v = 0; v < E / 4; ++v) {
+        const uint4 s = __ldg(reinterpret_cast<const uint4*>(map) + v * 32 + lane);
+        x[4 * v]     = scratch[W::phys(s.x)];
+        x[4 * v + 1] = scratch[W::phys(s.y)];
+        x[4 * v + 2] = scratch[W::phys(s.z)];
+        x[4 * v + 3] = scratch[W::phys(s.w)];
+    }
+    __syncwarp();
+}
+
+// acc[c] (+)= sum_d dig[d] * ak[d][c]   (dig from registers for the producing warp, from exch for the other)
+template <int LOGN, int ND, bool FROM_REGS, bool ADD>
+__device__ __forceinline__ void mac_auto(u32 (&acc)[(1 << LOGN) / 32], const u32 (&dg)[ND][(1 << LOGN) / 32], const uint4* exch,
+                                         const BrParams& P, const u32* ak, int c, int lane) {
+    constexpr int N = 1 << LOGN, E = N / 32;
+    const u32 Q = P.C.Q, Q2 = P.C.Q2;
+#pragma unroll
+    for (int v = 0; v < E / 4; ++v) {
+        uint4 k1[ND], dx[ND];
+#pragma unroll
+        for (int d = 0; d < ND; ++d) {
+            k1[d] = __ldg(reinterpret_cast<const uint4*>(ak + (size_t)(d * 2 + c) * N) + v * 32 + lane);
+            if (!FROM_REGS) dx[d] = exch[d * (N / 4) + v * 32 + lane];
+        }
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            u64 s = ADD ? (u64)acc[4 * v + e] : 0ull;
+#pragma unroll
+            for (int d = 0; d < ND; ++d) s = mad_wide(FROM_REGS ? dg[d][4 * v + e] : comp4(dx[d], e), comp4(k1[d], e), s);
+            acc[4 * v + e] = csub(reduce64(s, P.red_s, P.red_mu, Q), Q2);
+        }
+    }
+}
+
+// ---- scheduled kernel ------------------------------------------------------------------------------------------
+template <int LOGN, int LOGH, int ROWS, int CTS>
+__global__ void __launch_bounds__(64 * CTS, (LOGN <= 10 && ROWS <= 4) ? 3 : 1)
+br_sched_kernel(const __grid_constant__ BrParams P) {
+    using W         = WNtt<LOGN, LOGH>;
+    using S         = BrSmem<LOGN, LOGH, ROWS, CTS>;
+    constexpr int N = W::N, E = W::E, ND = ROWS / 2;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    S& sm = *reinterpret_cast<S*>(smem_raw);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int slot = warp >> 1, c = warp & 1;
+    for (int i = threadIdx.x; i < W::NB * 32; i += blockDim.x) {
+        sm.twB[i]  = P.twB[i];
+        sm.twiB[i] = P.twiB[i];
+    }
+    __syncthreads();
+    const u32 ct = blockIdx.x * CTS + slot;
+    if (ct >= P.count) return;
+    u32* scratch = sm.scratch[warp];
+    uint4* exch  = &sm.exch[slot][0][0];
+    u32 acc[E];
+    if (P.mode == 0) {
+        prologue<LOGN, LOGH>(acc, P, ct, scratch, sm.twB, c, lane);
+    } else {
+        const uint4* src = reinterpret_cast<const uint4*>(P.acc_io + ((size_t)ct * 2 + c) * N);
+#pragma unroll
+        for (int v = 0; v < E / 4; ++v) {
+            uint4 t        = src[v * 32 + lane];
+            acc[4 * v]     = t.x;
+            acc[4 * v + 1] = t.y;
+            acc[4 * v + 2] = t.z;
+            acc[4 * v + 3] = t.w;
+        }
+    }
+    const u32* ops      = P.sched + (size_t)ct * P.sched_stride;
+    const size_t kblock = (size_t)ROWS * 2 * N;
+    const size_t ablock = (size_t)ND * 2 * N;
+    for (u32 pc = 0;; ++pc) {
+        const u32 op = ops[pc];
+        const u32 ty = op & OP_MASK, arg = op & ~OP_MASK;
+        if (ty == OP_END) break;
+        if (ty == OP_EXT) {
+            u32 dg[ND][E];
+            digits_from_acc<LOGN, LOGH, ROWS>(acc, dg, P, scratch, sm.twB, sm.twiB, exch, c, lane);
+            pair_barrier(1 + slot);
+            mac_replace<LOGN, ROWS>(acc, dg, exch, P, P.bsk + (size_t)arg * kblock, c, lane);
+            pair_barrier(1 + slot);
+        } else if (ty == OP_PERM1) {
+            if (c == 1) permute_eval<LOGN, LOGH>(acc, scratch, P.automap + (size_t)arg * N, lane);
+        } else {  // OP_AUTO: Automorphism(a = 5^arg or 2N-5), rgsw-acc-lmkcdey.cpp:257-287
+            const u32* map = P.automap + (size_t)arg * N;
+            const u32* ak  = P.bsk + P.auto_off + (size_t)arg * ablock;
+            u32 dg[ND][E];
+            permute_eval<LOGN, LOGH>(acc, scratch, map, lane);
+            if (c == 0) {
+                W::inverse(acc, P.C, scratch, sm.twiB, P.twifull, lane);  // cta -> COEFFICIENT, canonical
+#pragma unroll
+                for (int r = 0; r < E; ++r) {
+                    u32 d[ND];
+                    decompose_coeff<ND>(acc[r], P.C.Q, P.qhalf, (int)P.gbits, d);
+#pragma unroll
+                    for (int k = 0; k < ND; ++k) dg[k][r] = d[k];
+                }
+#pragma unroll
+                for (int k = 0; k < ND; ++k) {
+                    W::template forward<1>(dg[k], P.C, scratch, sm.twB, P.twfull, lane);
+                    uint4* dst = exch + k * (N / 4);
+#pragma unroll
+                    for (int v = 0; v < E / 4; ++v)
+                        dst[v * 32 + lane] = make_uint4(dg[k][4 * v], dg[k][4 * v + 1], dg[k][4 * v + 2], dg[k][4 * v + 3]);
+                }
+                mac_auto<LOGN, ND, true, false>(acc, dg, exch, P, ak, 0, lane);  // acc[0] = sum dcta * ak[.][0]
+            }
+            pair_barrier(1 + slot);
+            if (c == 1) mac_auto<LOGN, ND, false, true>(acc, dg, exch, P, ak, 1, lane);  // acc[1] += sum dcta * ak[.][1]
+            pair_barrier(1 + slot);
+        }
+    }
+    if (P.mode == 0) {
+        epilogue<LOGN, LOGH>(acc, P, ct, scratch, sm.twiB, c, lane);
+    } else {
+        uint4* dst = reinterpret_cast<uint4*>(P.acc_io + ((size_t)ct * 2 + c) * N);
+#pragma unroll
+        for (int v = 0; v < E / 4; ++v)
+            dst[v * 32 + lane] = make_uint4(csub(acc[4 * v], P.C.Q), csub(acc[4 * v + 1], P.C.Q),
+                                            csub(acc[4 * v + 2], P.C.Q), csub(acc[4 * v + 3], P.C.Q));
+    }
+}

@@ -1,0 +1,239 @@
+"""GPU parity tests proper: the CUDA path (through the C ABI) against (1) the golden vectors the real reference
+produced, (2) the oracle on the same seeded inputs, (3) size-independent properties at BASELINE sizes.
+Bit-exact everywhere: this path is integer arithmetic (RoundqQ is IEEE double, reproduced exactly)."""
+import os
+
+import numpy as np
+import pytest
+
+from conftest import GOLD, gold_u64, load_gold
+import orclib
+from orclib import GATE, METHOD, OrcContext, P, hand_params, oracle
+
+pytestmark = pytest.mark.gpu
+
+
+def cuda_ctx_from_gold(d, method):
+    from fhe_b200.context import BinFHEContext
+    c = d["custom"]
+    ctx = BinFHEContext()
+    Q = ctx.L.luxb200_last_prime(c["bits"], 2 * c["N"])
+    ctx.GenerateFromParams(n=c["n"], N=c["N"], q=c["q"], Q=Q, qKS=c["qKS"], baseKS=c["baseKS"], baseG=c["baseG"],
+                           baseR=c["baseR"], numAutoKeys=c["numAutoKeys"], method=method)
+    ctx.BTKeyLoad(gold_u64(d["bsk"]), gold_u64(d["kskA"]), gold_u64(d["kskB"]))
+    return ctx
+
+
+def oracle_twin(ctx, method):
+    return OrcContext(hand_params(ctx.n, ctx.N, ctx.q, ctx.Q, ctx.qKS, ctx.baseKS, ctx.baseG, ctx.baseR,
+                                  ctx.numAutoKeys, METHOD[method]))
+
+
+# ---- NTT -------------------------------------------------------------------------------------------------------
+def test_ntt_golden_and_roundtrip():
+    from fhe_b200.context import NTTPlan
+    z = np.load(os.path.join(GOLD, "ntt.npz"))
+    for key in [k for k in z.files if k.startswith("q_")]:
+        _, bits, N = key.split("_")
+        Q, psi = [int(v) for v in z[key]]
+        x, X = z[f"x_{bits}_{N}"], z[f"X_{bits}_{N}"]
+        pl = NTTPlan(int(N), [Q], [psi])
+        got = pl.SwitchFormat(x, 0)
+        assert (got == X).all(), key
+        assert (pl.SwitchFormat(got, 1) == x).all(), key
+        pl.close()
+
+
+@pytest.mark.parametrize("bits,N,cnt", [(27, 1024, 4099), (29, 2048, 1031), (27, 512, 77), (28, 1024, 1), (25, 256, 5)])
+def test_ntt_u32_vs_oracle_ragged(bits, N, cnt):
+    """ragged batch sizes (not a multiple of the warps per CTA), both directions"""
+    from fhe_b200.context import NTTPlan
+    O = oracle()
+    Q = O.orc_last_prime(bits, 2 * N); psi = O.orc_root_of_unity(2 * N, Q)
+    rng = np.random.default_rng(bits * N)
+    x = rng.integers(0, Q, size=(cnt, N), dtype=np.uint64)
+    x[0, :] = Q - 1  # maximum residues
+    if cnt > 1:
+        x[1, :] = 0
+    pl = NTTPlan(N, [Q])
+    ref = x.copy(); O.orc_ntt(Q, psi, N, P(ref), cnt, 0, 8)
+    got = pl.SwitchFormat(x, 0)
+    assert (got == ref).all()
+    assert (pl.SwitchFormat(got, 1) == x).all()
+    pl.close()
+
+
+@pytest.mark.parametrize("bits,N,L,cnt", [(60, 4096, 3, 5), (60, 65536, 4, 2), (50, 16384, 2, 3), (37, 2048, 1, 9),
+                                          (60, 1024, 2, 3), (60, 131072, 1, 1)])
+def test_ntt_u64_dcrt_vs_oracle(bits, N, L, cnt):
+    """DCRTPoly::SwitchFormat shape: [count][L][N] with the ILDCRTParams moduli chain"""
+    from fhe_b200.context import NTTPlan
+    O = oracle()
+    q = np.zeros(L, np.uint64); psi = np.zeros(L, np.uint64)
+    O.orc_dcrt_chain(N, L, bits, P(q), P(psi))
+    rng = np.random.default_rng(N + L)
+    x = np.stack([np.stack([rng.integers(0, int(q[l]), size=N, dtype=np.uint64) for l in range(L)]) for _ in range(cnt)])
+    x[0, 0, :] = q[0] - np.uint64(1)
+    ref = x.copy()
+    for i in range(cnt):
+        for l in range(L):
+            O.orc_ntt(int(q[l]), int(psi[l]), N, P(ref[i, l]), 1, 0, 1)
+    pl = NTTPlan(N, q, psi)
+    got = pl.SwitchFormat(x, 0).reshape(x.shape)
+    assert (got == ref).all()
+    assert (pl.SwitchFormat(got, 1).reshape(x.shape) == x).all()
+    pl.close()
+
+
+# ---- binfhe: golden vectors of the real reference ---------------------------------------------------------------
+@pytest.mark.parametrize("method", ["GINX", "AP", "LMKCDEY"])
+def test_binfhe_golden(method):
+    d = load_gold(method)
+    ctx = cuda_ctx_from_gold(d, method)
+    a1, b1, a2, b2 = gold_u64(d["a1"]), gold_u64(d["b1"]), gold_u64(d["a2"]), gold_u64(d["b2"])
+    for g in ["AND", "OR", "NAND", "NOR", "XOR", "XNOR"]:
+        for ext in (0, 1):
+            (oa, ob), res = ctx.EvalBinGateBatch(g, (a1, b1), (a2, b2), bool(ext))
+            assert res.success, res.error
+            assert (oa == d[f"{g}_{ext}_a"]).all() and (ob == d[f"{g}_{ext}_b"]).all(), (g, ext)
+    (oa, ob), res = ctx.BootstrapBatch((a1, b1))
+    assert res.success and (oa == d["BOOT_a"]).all() and (ob == d["BOOT_b"]).all()
+    for g, k, pm in [("AND3", 3, 6), ("OR3", 3, 6), ("MAJORITY", 3, 4), ("AND4", 4, 8), ("OR4", 4, 8), ("CMUX", 3, 4)]:
+        (oa, ob), res = ctx.EvalBinGateMultiBatch(g, gold_u64(d[f"{g}_in_a"]), gold_u64(d[f"{g}_in_b"]), pm)
+        assert res.success, res.error
+        assert (oa == d[f"{g}_a"]).all() and (ob == d[f"{g}_b"]).all(), g
+    fa, fb = gold_u64(d["F_in_a"]), gold_u64(d["F_in_b"])
+    for name in ["neg", "per", "arb"]:
+        (oa, ob), res = ctx.EvalFuncBatch((fa, fb), gold_u64(d[f"F_{name}_lut"]))
+        assert res.success == (int(d[f"F_{name}_rc"][0]) == 0)
+        if res.success:
+            assert (oa == d[f"F_{name}_a"]).all() and (ob == d[f"F_{name}_b"]).all(), name
+    acc = ctx.BlindRotateBatch(a1[:1], gold_u64(d["ACC_in"]).reshape(1, 2, ctx.N))
+    assert (acc.reshape(-1) == d["ACC_out"]).all()
+    oa, ob = ctx.KeySwitchBatch((gold_u64(d["KS_in_a"]), gold_u64(d["KS_in_b"])))
+    assert (oa == d["KS_a"]).all() and (ob == d["KS_b"]).all()
+    assert (ctx.ModSwitchBatch(gold_u64(d["MS_in"]), ctx.qKS, ctx.Q) == d["MS_out"]).all()
+    ctx.close()
+
+
+# ---- binfhe: named parameter sets vs the oracle on seeded keys/inputs ---------------------------------------------
+def _seeded_inputs(oc, sk, cnt, base):
+    a = np.zeros((cnt, oc.p.n), np.uint64); b = np.zeros(cnt, np.uint64)
+    for i in range(cnt):
+        a[i], b[i] = oc.encrypt(sk, (i >> base) & 1, 1000 * (base + 1) + i)
+    return a, b
+
+
+@pytest.mark.parametrize("name,method,cnt", [("TOY", "GINX", 33), ("TOY", "AP", 9), ("TOY", "LMKCDEY", 9),
+                                             ("STD128", "GINX", 6), ("STD128_LMKCDEY", "LMKCDEY", 4)])
+def test_gates_vs_oracle(name, method, cnt):
+    from fhe_b200.context import BinFHEContext
+    ctx = BinFHEContext().GenerateBinFHEContext(name, method)
+    oc = oracle_twin(ctx, method)
+    sk, bsk, A, B = oc.keygen(seed=99, key_dist=getattr(ctx, "keyDist", 0))
+    ctx.BTKeyLoad(bsk, A, B)
+    a1, b1 = _seeded_inputs(oc, sk, cnt, 0)
+    a2, b2 = _seeded_inputs(oc, sk, cnt, 1)
+    # edge cases: an all-zero mask (every GINX step is X^0 - 1 = 0) and maximal residues
+    a1[0, :] = 0
+    a2[-1, :] = ctx.q - 1
+    for g in ["AND", "XNOR"]:
+        for ext in (False, True):
+            (oa, ob), res = ctx.EvalBinGateBatch(g, (a1, b1), (a2, b2), ext)
+            assert res.success, res.error
+            xa, xb = oc.evalbingate(g, a1, b1, a2, b2, ext)
+            assert (oa == xa).all() and (ob == xb).all(), (name, method, g, ext)
+    dec = [oc.decrypt(sk, oa[i], ob[i]) for i in range(1, cnt - 1)]
+    ctx.close(); oc.close()
+
+
+def test_std128_ap_gates_vs_oracle():
+    """STD128_AP: ~1 GB bootstrapping key, data-dependent key gather"""
+    from fhe_b200.context import BinFHEContext
+    from fhe_b200 import keygen as kg
+    ctx = BinFHEContext().GenerateBinFHEContext("STD128_AP", "AP")
+    ks = kg.keygen(ctx, seed=5)
+    ctx.BTKeyLoad(ks.bsk, ks.kskA, ks.kskB)
+    oc = oracle_twin(ctx, "AP")
+    oc.load(ks.bsk, ks.kskA, ks.kskB)
+    rng = np.random.default_rng(3)
+    m1 = rng.integers(0, 2, 4); m2 = rng.integers(0, 2, 4)
+    a1, b1 = kg.encrypt(ctx, ks.sk, m1, rng); a2, b2 = kg.encrypt(ctx, ks.sk, m2, rng)
+    (oa, ob), res = ctx.EvalBinGateBatch("OR", (a1, b1), (a2, b2))
+    assert res.success, res.error
+    xa, xb = oc.evalbingate("OR", a1, b1, a2, b2)
+    assert (oa == xa).all() and (ob == xb).all()
+    assert (kg.decrypt(ctx, ks.sk, oa, ob) == (m1 | m2)).all()
+    ctx.close(); oc.close()
+
+
+def test_error_behaviour():
+    """reference error behaviour: no keys -> error result; same ciphertext twice -> error; bad gate -> error"""
+    from fhe_b200.context import BinFHEContext
+    ctx = BinFHEContext().GenerateBinFHEContext("TOY", "GINX")
+    a = np.zeros((2, ctx.n), np.uint64); b = np.zeros(2, np.uint64)
+    (_, _), res = ctx.EvalBinGateBatch("AND", (a, b), (a.copy(), b.copy()))
+    assert not res.success and "Bootstrapping keys" in res.error and res.failed == 2
+    (_, _), res = ctx.EvalBinGateBatch("AND3", (a, b), (a.copy(), b.copy()))
+    assert not res.success
+    # empty batch is a no-op success
+    e = np.zeros((0, ctx.n), np.uint64); eb = np.zeros(0, np.uint64)
+    (oa, ob), res = ctx.EvalBinGateBatch("AND", (e, eb), (e.copy(), eb.copy()))
+    assert res.success and res.processed == 0 and oa.shape[0] == 0
+    ctx.close()
+
+
+# ---- full-size properties (BASELINE configs[2] shape) ---------------------------------------------------------------
+def test_std128_full_batch_properties():
+    """2^15 gates: decrypt == truth table for every gate on real encryptions; results independent of batch position
+    and chunking (same pair at different indices gives identical ciphertexts); device and host paths agree."""
+    import torch
+    from fhe_b200.context import BinFHEContext
+    from fhe_b200 import keygen as kg
+    ctx = BinFHEContext().GenerateBinFHEContext("STD128", "GINX")
+    ks = kg.keygen(ctx, seed=123)
+    ctx.BTKeyLoad(ks.bsk, ks.kskA, ks.kskB)
+    G = 1 << 15
+    rng = np.random.default_rng(7)
+    m1 = rng.integers(0, 2, G); m2 = rng.integers(0, 2, G)
+    a1, b1 = kg.encrypt(ctx, ks.sk, m1, rng); a2, b2 = kg.encrypt(ctx, ks.sk, m2, rng)
+    a1[G - 1], b1[G - 1], a2[G - 1], b2[G - 1] = a1[0], b1[0], a2[0], b2[0]
+    (oa, ob), res = ctx.EvalBinGateBatch("NAND", (a1, b1), (a2, b2))
+    assert res.success, res.error
+    dec = kg.decrypt(ctx, ks.sk, oa, ob)
+    exp = 1 - (m1 & m2); exp[G - 1] = exp[0]
+    assert (dec == exp).all()
+    assert (oa[0] == oa[G - 1]).all() and ob[0] == ob[G - 1]
+    # oracle spot check on 3 positions (start, middle, end)
+    oc = oracle_twin(ctx, "GINX"); oc.load(ks.bsk, ks.kskA, ks.kskB)
+    idx = np.array([0, G // 2 + 1, G - 2])
+    xa, xb = oc.evalbingate("NAND", a1[idx].copy(), b1[idx].copy(), a2[idx].copy(), b2[idx].copy())
+    assert (oa[idx] == xa).all() and (ob[idx] == xb).all()
+    # device-resident entry point gives the same bits
+    dev = torch.device("cuda", 0)
+    d = [torch.from_numpy(x.astype(np.uint32).view(np.int32)).to(dev) for x in (a1, b1, a2, b2)]
+    d_oa = torch.empty((G, ctx.n), dtype=torch.int32, device=dev); d_ob = torch.empty(G, dtype=torch.int32, device=dev)
+    torch.cuda.synchronize()
+    ctx.EvalBinGateBatchDev("NAND", d[0].data_ptr(), d[1].data_ptr(), d[2].data_ptr(), d[3].data_ptr(),
+                            d_oa.data_ptr(), d_ob.data_ptr(), G)
+    ctx.Synchronize()
+    assert (d_oa.cpu().numpy().view(np.uint32) == oa.astype(np.uint32)).all()
+    assert (d_ob.cpu().numpy().view(np.uint32) == ob.astype(np.uint32)).all()
+    ctx.close(); oc.close()
+
+
+def test_ntt_full_size_linearity():
+    """65536 polynomials at N=1024 (BASELINE configs[1]): NTT(a) + NTT(b) == NTT(a + b) and inverse(forward) == id"""
+    from fhe_b200.context import NTTPlan
+    O = oracle()
+    N, cnt = 1024, 65536
+    Q = O.orc_last_prime(27, 2 * N)
+    rng = np.random.default_rng(2)
+    a = rng.integers(0, Q, size=(cnt, N), dtype=np.uint64); b = rng.integers(0, Q, size=(cnt, N), dtype=np.uint64)
+    pl = NTTPlan(N, [Q])
+    A, B, S = pl.SwitchFormat(a, 0), pl.SwitchFormat(b, 0), pl.SwitchFormat((a + b) % np.uint64(Q), 0)
+    assert ((A + B) % np.uint64(Q) == S).all()
+    assert (pl.SwitchFormat(A, 1) == a).all()
+    ref = a[:64].copy(); O.orc_ntt(Q, O.orc_root_of_unity(2 * N, Q), N, P(ref), 64, 0, 8)
+    assert (A[:64] == ref).all()
+    pl.close()

@@ -1,0 +1,61 @@
+"""CPU: pin the plain-C oracle against the REAL reference (oracle/_ref/libref_shim.so) on the reference's own
+fresh keys.  Skipped where the prebuilt reference library is absent."""
+import numpy as np
+import pytest
+
+import orclib
+from orclib import GATE, OrcContext, P, RefContext
+
+pytestmark = pytest.mark.skipif(not orclib.ref_available(), reason="oracle/_ref/libref_shim.so not built")
+
+
+def test_primes_roots_ntt():
+    R, O = orclib.ref(), orclib.oracle()
+    rng = np.random.default_rng(1)
+    for bits, N in [(27, 1024), (29, 2048), (37, 2048), (60, 4096)]:
+        Q = R.ref_last_prime(bits, 2 * N)
+        assert Q == O.orc_last_prime(bits, 2 * N)
+        psi = R.ref_root_of_unity(2 * N, Q)
+        assert psi == O.orc_root_of_unity(2 * N, Q)
+        x = rng.integers(0, Q, size=(3, N), dtype=np.uint64)
+        a, b = x.copy(), x.copy()
+        R.ref_ntt(Q, psi, N, P(a), 3, 0, 1); O.orc_ntt(Q, psi, N, P(b), 3, 0, 1)
+        assert (a == b).all()
+        R.ref_ntt(Q, psi, N, P(a), 3, 1, 1); O.orc_ntt(Q, psi, N, P(b), 3, 1, 1)
+        assert (a == b).all() and (a == x).all()
+
+
+@pytest.mark.parametrize("method", ["GINX", "AP", "LMKCDEY"])
+def test_toy_gates_bootstrap_func(method):
+    R, O = orclib.ref(), orclib.oracle()
+    rc = RefContext("TOY", method)
+    rc.keygen()
+    oc = OrcContext(rc.p)
+    assert (oc.p.digitsG, oc.p.digitsKS, oc.p.psi) == (rc.p.digitsG, rc.p.digitsKS, rc.p.psi)
+    oc.load(rc.dump_bsk(), *rc.dump_ksk())
+    p, cnt = rc.p, 4
+    a1 = np.zeros((cnt, p.n), np.uint64); b1 = np.zeros(cnt, np.uint64); a2 = a1.copy(); b2 = b1.copy()
+    for i in range(cnt):
+        a1[i], b1[i] = rc.encrypt(i & 1); a2[i], b2[i] = rc.encrypt((i >> 1) & 1)
+    truth = {"AND": lambda x, y: x & y, "OR": lambda x, y: x | y, "XOR": lambda x, y: x ^ y,
+             "NAND": lambda x, y: 1 - (x & y)}
+    for g in truth:
+        for ext in (0, 1):
+            oa = np.zeros((cnt, p.N if ext else p.n), np.uint64); ob = np.zeros(cnt, np.uint64)
+            assert R.ref_evalbingate(rc.h, GATE[g], P(a1), P(b1), P(a2), P(b2), P(oa), P(ob), cnt, ext, 4) == 0
+            xa, xb = oc.evalbingate(g, a1, b1, a2, b2, bool(ext), threads=4)
+            assert (oa == xa).all() and (ob == xb).all(), (method, g, ext)
+            if not ext:  # the reference's own test tier: decrypt == truth table (UnitTestFHEW.cpp:380-420)
+                assert [rc.decrypt(xa[i], xb[i]) for i in range(cnt)] == [truth[g](i & 1, (i >> 1) & 1) for i in range(cnt)]
+    oa = np.zeros((cnt, p.n), np.uint64); ob = np.zeros(cnt, np.uint64); xa = oa.copy(); xb = ob.copy()
+    R.ref_bootstrap(rc.h, P(a1), P(b1), P(oa), P(ob), cnt, 4, 0, 4)
+    O.orc_bootstrap(oc.h, P(a1), P(b1), P(xa), P(xb), cnt, 4, 0, 4)
+    assert (oa == xa).all() and (ob == xb).all()
+    q, beta = p.q, R.ref_get_beta(rc.h)
+    pp = max(2, q // (2 * beta)); step = q // pp
+    for f in (lambda m: m % (pp // 2), lambda m: (m * m * m) % pp):
+        lut = np.array([(q // pp) * f(x // step) for x in range(q)], np.uint64)
+        r1 = R.ref_evalfunc(rc.h, P(a1), P(b1), P(lut), q, P(oa), P(ob), cnt, q, 4)
+        r2 = O.orc_evalfunc(oc.h, P(a1), P(b1), P(lut), q, beta, P(xa), P(xb), cnt, q, 4)
+        assert r1 == r2 and (r1 != 0 or ((oa == xa).all() and (ob == xb).all()))
+    rc.close(); oc.close()
