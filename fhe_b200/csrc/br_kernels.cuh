@@ -124,6 +124,7 @@ __device__ __forceinline__ void prologue(u32 (&acc)[(1 << LOGN) / 32], const BrP
         return;
     }
     const u32 b = P.b[ct], half = P.ctmod >> 1;
+    u32 m[E];
 #pragma unroll
     for (int r = 0; r < E; ++r) {
         const u32 j = lane + 32 * r;
@@ -132,9 +133,11 @@ __device__ __forceinline__ void prologue(u32 (&acc)[(1 << LOGN) / 32], const BrP
             const u32 jj = j / P.factor;
             if (jj < half) val = P.lut[(b + P.ctmod - jj) % P.ctmod];
         }
-        acc[r] = val;
+        m[r] = val;
     }
-    W::template forward<1>(acc, P.C, scratch, twB, P.twfull, lane);
+    W::template forward<1>(m, P.C, scratch, twB, P.twfull, lane);
+#pragma unroll
+    for (int r = 0; r < E; ++r) acc[r] = m[r];
 }
 
 // ---- epilogue: a' = Transpose(acc0) in coefficient form, b = coeff0(acc1) + b_add -----------------------

@@ -31,6 +31,7 @@ struct WNtt {
     static constexpr int E    = N / 32;
     static constexpr int LOGE = LOGN - 5;
     static constexpr int TB   = (E / 2 < 16) ? E / 2 : 16;  // largest in-thread stride of phase B
+    static constexpr int LOGTB = (TB == 16) ? 4 : (TB == 8) ? 3 : (TB == 4) ? 2 : 1;
     static constexpr int H    = 1 << LOGH;                  // Q < 2^(32-LOGH): values < H*Q fit in 32 bits
 
     __host__ __device__ static constexpr int offB(int t) {  // first entry of stage t in the lane-major table
@@ -77,18 +78,17 @@ struct WNtt {
         const u32 Q = C.Q, Q2 = C.Q2;
         int bound = B0;
 #pragma unroll
-        for (int tr = E / 2; tr >= 1; tr >>= 1) {
+        for (int s = LOGE - 1; s >= 0; --s) {  // in-register stride tr = 2^s  (global half-size t = 32 tr)
             if (bound + 2 > H) {
 #pragma unroll
                 for (int r = 0; r < E; ++r) x[r] = reduce_2q(x[r], C.mu32, Q);
                 bound = 2;
             }
-            const int m = E / (2 * tr);
 #pragma unroll
-            for (int i = 0; i < m; ++i) {
-                const uint2 w = C.twA[m + i];
-#pragma unroll
-                for (int r = 2 * i * tr; r < 2 * i * tr + tr; ++r) ct(x[r], x[r + tr], w.x, w.y, Q, Q2);
+            for (int qq = 0; qq < E / 2; ++qq) {
+                const int tr = 1 << s, i = qq >> s, r = (i << (s + 1)) | (qq & (tr - 1));
+                const uint2 w = C.twA[(E >> (s + 1)) + i];
+                ct(x[r], x[r + tr], w.x, w.y, Q, Q2);
             }
             bound += 2;
         }
@@ -116,18 +116,17 @@ struct WNtt {
         __syncwarp();
         load_B(sm, x, lane);
 #pragma unroll
-        for (int t = TB; t >= 1; t >>= 1) {
+        for (int s = LOGTB; s >= 0; --s) {  // in-register stride t = 2^s
             if (bound + 2 > H) {
 #pragma unroll
                 for (int r = 0; r < E; ++r) x[r] = reduce_2q(x[r], C.mu32, Q);
                 bound = 2;
             }
-            const int g = E / (2 * t);
 #pragma unroll
-            for (int i = 0; i < g; ++i) {
+            for (int qq = 0; qq < E / 2; ++qq) {
+                const int t = 1 << s, i = qq >> s, r = (i << (s + 1)) | (qq & (t - 1));
                 const uint2 w = twB[(offB(t) + i) * 32 + lane];
-#pragma unroll
-                for (int r = 2 * i * t; r < 2 * i * t + t; ++r) ct(x[r], x[r + t], w.x, w.y, Q, Q2);
+                ct(x[r], x[r + t], w.x, w.y, Q, Q2);
             }
             bound += 2;
         }
@@ -149,15 +148,13 @@ struct WNtt {
         const u32 Q = C.Q;
         int bound   = 2;  // 2*bound <= H holds on entry to every stage
 #pragma unroll
-        for (int t = 1; t <= TB; t <<= 1) {
+        for (int s = 0; s <= LOGTB; ++s) {
             const bool red = 4 * bound > H;
-            const int g    = E / (2 * t);
 #pragma unroll
-            for (int i = 0; i < g; ++i) {
+            for (int qq = 0; qq < E / 2; ++qq) {
+                const int t = 1 << s, i = qq >> s, r = (i << (s + 1)) | (qq & (t - 1));
                 const uint2 w = twiB[(offB(t) + i) * 32 + lane];
-#pragma unroll
-                for (int r = 2 * i * t; r < 2 * i * t + t; ++r)
-                    gs(x[r], x[r + t], w.x, w.y, Q, (u32)bound * Q, red, C.mu32);
+                gs(x[r], x[r + t], w.x, w.y, Q, (u32)bound * Q, red, C.mu32);
             }
             bound = red ? 2 : 2 * bound;
         }
@@ -183,15 +180,13 @@ struct WNtt {
             }
         }
 #pragma unroll
-        for (int tr = 1; tr < E / 2; tr <<= 1) {
+        for (int s = 0; s < LOGE - 1; ++s) {
             const bool red = 4 * bound > H;
-            const int m    = E / (2 * tr);
 #pragma unroll
-            for (int i = 0; i < m; ++i) {
-                const uint2 w = C.twiA[m + i];
-#pragma unroll
-                for (int r = 2 * i * tr; r < 2 * i * tr + tr; ++r)
-                    gs(x[r], x[r + tr], w.x, w.y, Q, (u32)bound * Q, red, C.mu32);
+            for (int qq = 0; qq < E / 2; ++qq) {
+                const int tr = 1 << s, i = qq >> s, r = (i << (s + 1)) | (qq & (tr - 1));
+                const uint2 w = C.twiA[(E >> (s + 1)) + i];
+                gs(x[r], x[r + tr], w.x, w.y, Q, (u32)bound * Q, red, C.mu32);
             }
             bound = red ? 2 : 2 * bound;
         }
