@@ -16,7 +16,7 @@ struct BrSmem {
 };
 
 // ---- digit pipeline: INTT -> decompose -> NTT -> publish (rows 2k+c) -------------------------------------
-template <int LOGN, int LOGH, int ROWS>
+template <int LOGN, int LOGH, int ROWS, bool CTA_SYNC = false>
 __device__ __forceinline__ void digits_from_acc(const u32 (&acc)[(1 << LOGN) / 32], u32 (&dg)[ROWS / 2][(1 << LOGN) / 32],
                                                 const BrParams& P, u32* scratch, const uint2* twB, const uint2* twiB,
                                                 uint4* exch /* [ROWS][N/4] */, int c, int lane) {
@@ -35,6 +35,7 @@ __device__ __forceinline__ void digits_from_acc(const u32 (&acc)[(1 << LOGN) / 3
     }
 #pragma unroll
     for (int k = 0; k < ROWS / 2; ++k) {
+        if (CTA_SYNC) __syncthreads();  // keep the CTA's warps in the same code window (instruction-cache sharing)
         W::template forward<1>(dg[k], P.C, scratch, twB, P.twfull, lane);
         uint4* dst = exch + (2 * k + c) * (W::N / 4);
 #pragma unroll
@@ -221,7 +222,7 @@ br_ginx_kernel(const __grid_constant__ BrParams P) {
         const u32 ai = arow[i];
         const u32 ap = ((P.ctmod - ai) % P.ctmod) * P.amul;  // (-a_i mod q) * (2N/q); ap = 0 -> monomials are 0
         u32 dg[ROWS / 2][E];
-        digits_from_acc<LOGN, LOGH, ROWS>(acc, dg, P, scratch, sm.twB, sm.twiB, exch, c, lane);
+        digits_from_acc<LOGN, LOGH, ROWS, false>(acc, dg, P, scratch, sm.twB, sm.twiB, exch, c, lane);
         __syncthreads();
         const u32* ek1 = P.bsk + (size_t)(2 * i) * kblock;
         const u32* mp  = P.mono + (size_t)ap * N;
