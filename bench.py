@@ -119,7 +119,7 @@ def run_reference(args, rank, world):
         return
     kind, orclib = load_checker()
     cores = os.cpu_count() or 1
-    gates = args.ref_gates or cores * 2
+    gates = args.ref_gates or cores * 4
     fn = cpu_time_gates(kind, orclib, gates, cores)
     for _ in range(args.warmup):
         fn()
@@ -173,21 +173,15 @@ def main():
         ks = kg.keygen(ctx, seed=2026)
         sk = ks.sk
     if world > 1:
-        t_bsk = torch.empty(bsk_len, dtype=torch.int64, device=dev)
-        t_kA = torch.empty(ksk_rows * n, dtype=torch.int64, device=dev)
-        t_kB = torch.empty(ksk_rows, dtype=torch.int64, device=dev)
-        t_sk = torch.empty(n, dtype=torch.int64, device=dev)
-        if rank == 0:
-            t_bsk.copy_(torch.from_numpy(ks.bsk.view(np.int64)))
-            t_kA.copy_(torch.from_numpy(ks.kskA.view(np.int64)))
-            t_kB.copy_(torch.from_numpy(ks.kskB.view(np.int64)))
-            t_sk.copy_(torch.from_numpy(ks.sk))
-        for t in (t_bsk, t_kA, t_kB, t_sk):
-            dist.broadcast(t, 0)
+        from fhe_b200 import parallel as par
+        lengths = {"bsk": bsk_len, "kskA": ksk_rows * n, "kskB": ksk_rows, "sk": n}
+        arrays = {"bsk": ks.bsk, "kskA": ks.kskA, "kskB": ks.kskB, "sk": ks.sk} if rank == 0 else None
+        keys = par.broadcast_keys(arrays, lengths, src=0, device=dev)      # NCCL over NVLink, once
         torch.cuda.synchronize()
-        ctx.BTKeyLoad(t_bsk.data_ptr(), t_kA.data_ptr(), t_kB.data_ptr(), on_device=True)
-        sk = t_sk.cpu().numpy()
-        del t_bsk, t_kA, t_kB
+        ctx.BTKeyLoad(keys["bsk"].data_ptr(), keys["kskA"].data_ptr(), keys["kskB"].data_ptr(), on_device=True)
+        sk = keys["sk"].cpu().numpy()
+        del keys
+        torch.cuda.empty_cache()
     else:
         ctx.BTKeyLoad(ks.bsk, ks.kskA, ks.kskB)
 
@@ -306,7 +300,7 @@ def main():
     if not args.no_cpu_baseline:
         kind, orclib = load_checker()
         cores = os.cpu_count() or 1
-        gates = cores * 2
+        gates = cores * 8
         fn = cpu_time_gates(kind, orclib, gates, cores)
         sec = fn()
         cpu_baseline = {"value": gates / sec, "unit": "bootstraps/s", "cores": cores, "kind": kind,
