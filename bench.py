@@ -119,7 +119,7 @@ def run_reference(args, rank, world):
         return
     kind, orclib = load_checker()
     cores = os.cpu_count() or 1
-    gates = args.ref_gates or cores * 4
+    gates = args.ref_gates or cores * 16
     fn = cpu_time_gates(kind, orclib, gates, cores)
     for _ in range(args.warmup):
         fn()
@@ -300,7 +300,7 @@ def main():
     if not args.no_cpu_baseline:
         kind, orclib = load_checker()
         cores = os.cpu_count() or 1
-        gates = cores * 8
+        gates = cores * 32
         fn = cpu_time_gates(kind, orclib, gates, cores)
         sec = fn()
         cpu_baseline = {"value": gates / sec, "unit": "bootstraps/s", "cores": cores, "kind": kind,
