@@ -1,0 +1,123 @@
+#!/usr/bin/env python
+"""Secondary workloads of BASELINE.json (configs[1], [3], [4]); one JSON line per workload.
+  python bench_extra.py [ntt32] [ntt64] [methods]
+Device-resident data, CUDA events on the library stream, >= 3 warm-ups; data sets exceed the 126 MB L2."""
+import json
+import os
+import sys
+import time
+
+import numpy as np
+import torch
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+from fhe_b200 import keygen as kg, lib as _l  # noqa: E402
+from fhe_b200.context import BinFHEContext, NTTPlan  # noqa: E402
+
+PEAKS = {}
+try:
+    PEAKS = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+except Exception:
+    pass
+HBM = PEAKS.get("hbm_gbs", 6650.0)
+
+
+def ntt32(N, bits, count, iters=10):
+    L = _l.load()
+    Q = L.luxb200_last_prime(bits, 2 * N)
+    pl = NTTPlan(N, [Q])
+    x = torch.randint(0, Q, (count, N), dtype=torch.int32, device="cuda")
+    torch.cuda.synchronize()
+    res = {}
+    for inv in (0, 1):
+        for _ in range(3):
+            pl.SwitchFormatDev(x.data_ptr(), count, inv, 4)
+        pl.Sync()
+        ms = []
+        for _ in range(iters):
+            pl.SwitchFormatDev(x.data_ptr(), count, inv, 4)
+            ms.append(pl.LastMs())
+        t = float(np.median(ms)) * 1e-3
+        bf = count * (N // 2) * (N.bit_length() - 1)
+        gbs = count * N * 4 * 2 / t / 1e9
+        res["inverse" if inv else "forward"] = {"ms": t * 1e3, "Gbutterfly_s": bf / t / 1e9, "GBs": gbs, "frac_hbm": gbs / HBM}
+    pl.close()
+    return {"workload": f"batched NTT u32 N={N} Q={bits}-bit x{count}", "bound": "hbm", "peak_gbs": HBM, **res}
+
+
+def ntt64(N, Lm, cnt, bits=60, iters=5):
+    L = _l.load()
+    q = [L.luxb200_last_prime(bits, 2 * N)]
+    for _ in range(Lm - 1):
+        q.append(L.luxb200_previous_prime(q[-1], 2 * N))
+    pl = NTTPlan(N, q)
+    x = torch.randint(0, 2**59, (cnt, Lm, N), dtype=torch.int64, device="cuda")
+    torch.cuda.synchronize()
+    res = {}
+    for inv in (0, 1):
+        for _ in range(3):
+            pl.SwitchFormatDev(x.data_ptr(), cnt, inv, 8)
+        pl.Sync()
+        ms = []
+        for _ in range(iters):
+            pl.SwitchFormatDev(x.data_ptr(), cnt, inv, 8)
+            ms.append(pl.LastMs())
+        t = float(np.median(ms)) * 1e-3
+        bf = cnt * Lm * (N // 2) * (N.bit_length() - 1)
+        gbs = cnt * Lm * N * 8 * 2 / t / 1e9
+        res["inverse" if inv else "forward"] = {"ms": t * 1e3, "Gbutterfly_s": bf / t / 1e9, "algorithmic_GBs": gbs,
+                                                 "frac_hbm_algorithmic": gbs / HBM}
+    pl.close()
+    return {"workload": f"DCRT NTT u64 N={N} L={Lm} x{cnt} ({bits}-bit primes)", **res}
+
+
+def method_gates(name, method, G, fn="gate"):
+    ctx = BinFHEContext().GenerateBinFHEContext(name, method)
+    ks = kg.keygen(ctx, seed=77)
+    ctx.BTKeyLoad(ks.bsk, ks.kskA, ks.kskB)
+    rng = np.random.default_rng(5)
+    out = {"workload": f"{name}/{method} {fn} x{G}"}
+    if fn == "gate":
+        m1 = rng.integers(0, 2, G); m2 = rng.integers(0, 2, G)
+        a1, b1 = kg.encrypt(ctx, ks.sk, m1, rng); a2, b2 = kg.encrypt(ctx, ks.sk, m2, rng)
+        ctx.EvalBinGateBatch("AND", (a1[:64], b1[:64]), (a2[:64], b2[:64]))
+        t0 = time.perf_counter()
+        (oa, ob), res = ctx.EvalBinGateBatch("AND", (a1, b1), (a2, b2))
+        dt = time.perf_counter() - t0
+        assert res.success, res.error
+        out["decrypt_errors"] = int((kg.decrypt(ctx, ks.sk, oa, ob) != (m1 & m2)).sum())
+        out["bootstraps_per_s_e2e"] = G / dt
+        out.update(ctx.LastTiming())
+    else:  # EvalFunc, periodic LUT (2 bootstraps per call), p = q / 256
+        p = max(2, ctx.q // 256)
+        lut = ctx.GenerateLUTviaFunction(lambda m, pp: m % (pp // 2) if pp > 2 else 0, p)
+        m = rng.integers(0, p, G)
+        a, b = kg.encrypt(ctx, ks.sk, m, rng, p=p)
+        ctx.EvalFuncBatch((a[:64], b[:64]), lut)
+        t0 = time.perf_counter()
+        (oa, ob), res = ctx.EvalFuncBatch((a, b), lut)
+        dt = time.perf_counter() - t0
+        assert res.success, res.error
+        exp = np.array([(int(v) % (p // 2)) if p > 2 else 0 for v in m])
+        out["decrypt_errors"] = int((kg.decrypt(ctx, ks.sk, oa, ob, p=p) != exp).sum())
+        out["evalfunc_per_s_e2e"] = G / dt
+        out["bootstraps_per_s_e2e"] = 2 * G / dt
+    ctx.close()
+    return out
+
+
+if __name__ == "__main__":
+    which = sys.argv[1:] or ["ntt32", "ntt64", "methods"]
+    if "ntt32" in which:
+        print(json.dumps(ntt32(1024, 27, 65536)))
+        print(json.dumps(ntt32(2048, 29, 65536)))
+    if "ntt64" in which:
+        print(json.dumps(ntt64(65536, 32, 64)))
+        print(json.dumps(ntt64(16384, 16, 64)))
+        print(json.dumps(ntt64(4096, 8, 512)))
+    if "methods" in which:
+        print(json.dumps(method_gates("STD128_LMKCDEY", "LMKCDEY", 16384)))
+        print(json.dumps(method_gates("STD128_AP", "AP", 4096)))
+        print(json.dumps(method_gates("STD128_LMKCDEY", "LMKCDEY", 16384, "func")))
+        print(json.dumps(method_gates("STD128_AP", "AP", 4096, "func")))

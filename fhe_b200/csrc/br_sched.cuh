@@ -120,8 +120,12 @@ __device__ __forceinline__ void mac_auto(u32 (&acc)[(1 << LOGN) / 32], const u32
 }
 
 // ---- scheduled kernel ------------------------------------------------------------------------------------------
+// One 2*CTS-warp CTA per SM, like br_ginx_kernel.  Ciphertexts walk their own op lists, but the CTA advances in
+// rounds with exactly two CTA-wide barriers per round whatever the op type, so the warps of an SM sub-partition stay
+// in the same code window (instruction-cache sharing) and the exchange buffer is race-free.  A ciphertext whose
+// list is exhausted idles at the barriers until every list in the CTA is done (op counts differ by a few percent).
 template <int LOGN, int LOGH, int ROWS, int CTS>
-__global__ void __launch_bounds__(64 * CTS, (LOGN <= 10 && ROWS <= 4) ? 3 : 1)
+__global__ void __launch_bounds__(64 * CTS, 1)
 br_sched_kernel(const __grid_constant__ BrParams P) {
     using W         = WNtt<LOGN, LOGH>;
     using S         = BrSmem<LOGN, LOGH, ROWS, CTS>;
@@ -135,8 +139,9 @@ br_sched_kernel(const __grid_constant__ BrParams P) {
         sm.twiB[i] = P.twiB[i];
     }
     __syncthreads();
-    const u32 ct = blockIdx.x * CTS + slot;
-    if (ct >= P.count) return;
+    const u32 ct_raw = blockIdx.x * CTS + slot;
+    const bool live  = ct_raw < P.count;
+    const u32 ct     = live ? ct_raw : P.count - 1;
     u32* scratch = sm.scratch[warp];
     uint4* exch  = &sm.exch[slot][0][0];
     u32 acc[E];
@@ -156,23 +161,21 @@ br_sched_kernel(const __grid_constant__ BrParams P) {
     const u32* ops      = P.sched + (size_t)ct * P.sched_stride;
     const size_t kblock = (size_t)ROWS * 2 * N;
     const size_t ablock = (size_t)ND * 2 * N;
-    for (u32 pc = 0;; ++pc) {
-        const u32 op = ops[pc];
-        const u32 ty = op & OP_MASK, arg = op & ~OP_MASK;
-        if (ty == OP_END) break;
+    bool done = !live;
+    u32 pc    = 0;
+#pragma unroll 1
+    for (;;) {
+        u32 op = done ? (u32)OP_END : ops[pc];
+        if ((op & OP_MASK) == OP_END) done = true;
+        if (__syncthreads_and(done)) break;
+        const u32 ty = done ? (u32)OP_END : (op & OP_MASK), arg = op & ~OP_MASK;
+        u32 dg[ND][E];
         if (ty == OP_EXT) {
-            u32 dg[ND][E];
             digits_from_acc<LOGN, LOGH, ROWS>(acc, dg, P, scratch, sm.twB, sm.twiB, exch, c, lane);
-            pair_barrier(1 + slot);
-            mac_replace<LOGN, ROWS>(acc, dg, exch, P, P.bsk + (size_t)arg * kblock, c, lane);
-            pair_barrier(1 + slot);
         } else if (ty == OP_PERM1) {
             if (c == 1) permute_eval<LOGN, LOGH>(acc, scratch, P.automap + (size_t)arg * N, lane);
-        } else {  // OP_AUTO: Automorphism(a = 5^arg or 2N-5), rgsw-acc-lmkcdey.cpp:257-287
-            const u32* map = P.automap + (size_t)arg * N;
-            const u32* ak  = P.bsk + P.auto_off + (size_t)arg * ablock;
-            u32 dg[ND][E];
-            permute_eval<LOGN, LOGH>(acc, scratch, map, lane);
+        } else if (ty == OP_AUTO) {  // Automorphism(a = 5^arg or 2N-5), rgsw-acc-lmkcdey.cpp:257-287
+            permute_eval<LOGN, LOGH>(acc, scratch, P.automap + (size_t)arg * N, lane);
             if (c == 0) {
                 W::inverse(acc, P.C, scratch, sm.twiB, P.twifull, lane);  // cta -> COEFFICIENT, canonical
 #pragma unroll
@@ -190,13 +193,18 @@ br_sched_kernel(const __grid_constant__ BrParams P) {
                     for (int v = 0; v < E / 4; ++v)
                         dst[v * 32 + lane] = make_uint4(dg[k][4 * v], dg[k][4 * v + 1], dg[k][4 * v + 2], dg[k][4 * v + 3]);
                 }
-                mac_auto<LOGN, ND, true, false>(acc, dg, exch, P, ak, 0, lane);  // acc[0] = sum dcta * ak[.][0]
+                mac_auto<LOGN, ND, true, false>(acc, dg, exch, P, P.bsk + P.auto_off + (size_t)arg * ablock, 0, lane);
             }
-            pair_barrier(1 + slot);
-            if (c == 1) mac_auto<LOGN, ND, false, true>(acc, dg, exch, P, ak, 1, lane);  // acc[1] += sum dcta * ak[.][1]
-            pair_barrier(1 + slot);
         }
+        __syncthreads();
+        if (ty == OP_EXT) {
+            mac_replace<LOGN, ROWS>(acc, dg, exch, P, P.bsk + (size_t)arg * kblock, c, lane);
+        } else if (ty == OP_AUTO && c == 1) {
+            mac_auto<LOGN, ND, false, true>(acc, dg, exch, P, P.bsk + P.auto_off + (size_t)arg * ablock, 1, lane);
+        }
+        if (!done) ++pc;
     }
+    if (!live) return;
     if (P.mode == 0) {
         epilogue<LOGN, LOGH>(acc, P, ct, scratch, sm.twiB, c, lane);
     } else {
