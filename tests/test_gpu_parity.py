@@ -64,7 +64,8 @@ def test_ntt_u32_vs_oracle_ragged(bits, N, cnt):
 
 
 @pytest.mark.parametrize("bits,N,L,cnt", [(60, 4096, 3, 5), (60, 65536, 4, 2), (50, 16384, 2, 3), (37, 2048, 1, 9),
-                                          (60, 1024, 2, 3), (60, 131072, 1, 1)])
+                                          (60, 1024, 2, 3), (60, 131072, 1, 1), (60, 32768, 3, 4), (60, 65536, 8, 4),
+                                          (59, 131072, 2, 6), (61, 16384, 1, 2), (60, 16384, 5, 24)])
 def test_ntt_u64_dcrt_vs_oracle(bits, N, L, cnt):
     """DCRTPoly::SwitchFormat shape: [count][L][N] with the ILDCRTParams moduli chain"""
     from fhe_b200.context import NTTPlan
