@@ -69,7 +69,13 @@ def ntt64(N, Lm, cnt, bits=60, iters=5):
         res["inverse" if inv else "forward"] = {"ms": t * 1e3, "Gbutterfly_s": bf / t / 1e9, "algorithmic_GBs": gbs,
                                                  "frac_hbm_algorithmic": gbs / HBM}
     pl.close()
-    return {"workload": f"DCRT NTT u64 N={N} L={Lm} x{cnt} ({bits}-bit primes)", **res}
+    import ctypes
+    pk = ctypes.c_double(0)
+    L.luxb200_intpipe_probe64(0, ctypes.byref(pk))
+    for k in res:
+        res[k]["frac_intpipe"] = res[k]["Gbutterfly_s"] * 1e9 / pk.value if pk.value else None
+    return {"workload": f"DCRT NTT u64 N={N} L={Lm} x{cnt} ({bits}-bit primes)",
+            "intpipe_peak_Gbutterfly_s": pk.value / 1e9, **res}
 
 
 def method_gates(name, method, G, fn="gate"):

@@ -6,7 +6,7 @@ import os
 import numpy as np
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-SO_PATH = os.path.join(HERE, "libluxb200.so")
+SO_PATH = os.environ.get("LUXB200_SO") or os.path.join(HERE, "libluxb200.so")   # override: A/B builds when profiling
 
 VP, U64, U32, INT = C.c_void_p, C.c_uint64, C.c_uint32, C.c_int
 
@@ -61,6 +61,7 @@ SIGNATURES = {
     "luxb200_last_timing": (INT, [VP, VP]),
     "luxb200_launch_count": (U64, [VP]),
     "luxb200_intpipe_probe": (INT, [INT, C.POINTER(C.c_double), C.POINTER(C.c_double)]),
+    "luxb200_intpipe_probe64": (INT, [INT, C.POINTER(C.c_double)]),
 }
 
 _lib = None

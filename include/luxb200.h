@@ -138,6 +138,9 @@ uint64_t luxb200_launch_count(luxb200_ctx* ctx);
 
 /* ---- integer-pipe roofline probe: measured IMAD-class issue rate of this GPU (ops/s) ------------------- */
 int luxb200_intpipe_probe(int device, double* imad_per_s, double* mixed_per_s);
+/* 64-bit Shoup butterflies per second on register-resident data: the integer-pipe roofline of the u64 NTT
+ * (replaces nothing in the reference; measurement only) */
+int luxb200_intpipe_probe64(int device, double* bfly64_per_s);
 
 #ifdef __cplusplus
 }
