@@ -148,6 +148,13 @@ class BinFHEContext:
         _l.check(self.L.luxb200_blind_rotate_batch(self.h, _l.ptr(a), amod or self.q, _l.ptr(acc), a.shape[0]))
         return acc
 
+    def ExternalProductBatch(self, rgsw, rlwe):
+        """Backend::ExternalProductBatch (backend.h:185-194): rgsw [count][rows][2][N], rlwe [count][2][N], EVALUATION."""
+        rgsw, rlwe = self._u64(rgsw), self._u64(rlwe)
+        out = np.empty_like(rlwe)
+        _l.check(self.L.luxb200_external_product_batch(self.h, _l.ptr(rgsw), _l.ptr(rlwe), _l.ptr(out), rlwe.shape[0]))
+        return out
+
     def KeySwitchBatch(self, ct):
         a, b = map(self._u64, ct)
         cnt = len(b)

@@ -49,6 +49,11 @@ SIGNATURES = {
     "luxb200_bootstrap_batch": (INT, [VP, VP, VP, VP, VP, U64, U64, INT]),
     "luxb200_evalfunc_batch": (INT, [VP, VP, VP, VP, U64, U64, VP, VP, U64, U64]),
     "luxb200_blind_rotate_batch": (INT, [VP, VP, U64, VP, U64]),
+    "luxb200_external_product_batch": (INT, [VP, VP, VP, VP, U64]),
+    "luxb200_dev_alloc": (INT, [INT, U64, C.POINTER(VP)]),
+    "luxb200_dev_free": (INT, [INT, VP]),
+    "luxb200_dev_copy": (INT, [INT, VP, VP, U64, INT]),
+    "luxb200_dev_mem_info": (INT, [INT, C.POINTER(U64), C.POINTER(U64)]),
     "luxb200_keyswitch_batch": (INT, [VP, VP, VP, VP, VP, U64]),
     "luxb200_modswitch_batch": (INT, [VP, U64, U64, VP, VP, U64]),
     "luxb200_ntt_plan_create": (INT, [U32, U32, VP, VP, INT, C.POINTER(VP)]),

@@ -1,0 +1,98 @@
+// backend_b200.h — lux::fhe::backend::BackendB200: the B200 implementation of the reference's backend seam
+// (src/binfhe/include/backend/backend.h:73-247), built on the C ABI of libluxb200.so (include/luxb200.h).
+//
+// This is host-side glue written against the reference's own headers; it is compiled by host/Makefile with
+// -I/root/reference/src/... and linked to the reference library built by oracle/Makefile.  It contains no
+// arithmetic: every virtual packs the reference's containers into flat uint64 arrays, calls one luxb200_* entry
+// point, and unpacks.  Type() reports BackendType::CUDA, so `BackendRegistry::Instance().Get(BackendType::CUDA)`
+// (backend.cpp:266-270) finds it after RegisterB200().
+#pragma once
+#include <luxb200.h>
+
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "backend/backend.h"
+#include "binfhecontext.h"
+
+namespace lux::fhe {
+namespace backend {
+
+class BackendB200 final : public Backend {
+public:
+    explicit BackendB200(int device = 0);
+    ~BackendB200() override;
+
+    // Create the device context for cc's parameters and upload cc's refresh and switching keys (after BTKeyGen).
+    // Throws lux::fhe::config_error-style std::runtime_error on failure; there is no CPU fallback.
+    void Bind(BinFHEContext& cc);
+    bool IsBound() const { return h_ != nullptr; }
+    luxb200_ctx* handle() const { return h_; }
+    int device() const { return device_; }
+
+    BackendType Type() const override { return BackendType::CUDA; }
+    std::string Name() const override { return "B200 (libluxb200, sm_100a)"; }
+    bool IsAvailable() const override;
+    size_t MaxBatchSize() const override { return size_t(1) << 24; }
+    size_t DeviceMemory() const override;
+
+    DeviceBuffer Allocate(size_t bytes) override;
+    void Free(DeviceBuffer& buffer) override;
+    void CopyToDevice(const void* host_ptr, DeviceBuffer& device_buffer, size_t bytes) override;
+    void CopyToHost(const DeviceBuffer& device_buffer, void* host_ptr, size_t bytes) override;
+    void Synchronize() override;
+
+    void BlindRotate(const std::shared_ptr<RingGSWCryptoParams>& params, const LWECiphertext& ct, const RingGSWACCKey& ek,
+                     RLWECiphertext& acc) override;
+    void ExternalProduct(const std::shared_ptr<RingGSWCryptoParams>& params, const RingGSWEvalKey& rgsw,
+                         const RLWECiphertext& rlwe, RLWECiphertext& result) override;
+    void KeySwitch(const std::shared_ptr<LWECryptoParams>& params, const LWECiphertext& ct, const LWESwitchingKey& ks,
+                   LWECiphertext& result) override;
+    void ModSwitch(const std::shared_ptr<LWECryptoParams>& params, const LWECiphertext& ct, LWECiphertext& result) override;
+
+    void BlindRotateBatch(const std::shared_ptr<RingGSWCryptoParams>& params, const std::vector<LWECiphertext>& cts,
+                          const RingGSWACCKey& ek, std::vector<RLWECiphertext>& accs) override;
+    void ExternalProductBatch(const std::shared_ptr<RingGSWCryptoParams>& params, const std::vector<RingGSWEvalKey>& rgsws,
+                              const std::vector<RLWECiphertext>& rlwes, std::vector<RLWECiphertext>& results) override;
+    void KeySwitchBatch(const std::shared_ptr<LWECryptoParams>& params, const std::vector<LWECiphertext>& cts,
+                        const LWESwitchingKey& ks, std::vector<LWECiphertext>& results) override;
+    void ModSwitchBatch(const std::shared_ptr<LWECryptoParams>& params, const std::vector<LWECiphertext>& cts,
+                        std::vector<LWECiphertext>& results) override;
+
+    // Packed formats: the canonical flat layouts of include/luxb200.h, resident in device memory (uint64).
+    DeviceBuffer PackBootstrappingKey(const RingGSWACCKey& ek) override;
+    void UnpackBootstrappingKey(const DeviceBuffer& packed, RingGSWACCKey& ek) override;
+    DeviceBuffer PackCiphertexts(const std::vector<LWECiphertext>& cts) override;     // [count][n+1]: a then b
+    void UnpackCiphertexts(const DeviceBuffer& packed, std::vector<LWECiphertext>& cts) override;
+
+    // Gate-level entry points used by the batch API bodies (host/batch_b200.cpp)
+    void EvalBinGate(BINGATE gate, const std::vector<LWECiphertext>& ct1, const std::vector<LWECiphertext>& ct2,
+                     std::vector<LWECiphertext>& out);
+    void EvalBinGateMulti(BINGATE gate, const std::vector<std::vector<LWECiphertext>>& cts, std::vector<LWECiphertext>& out);
+    void Bootstrap(const std::vector<LWECiphertext>& in, std::vector<LWECiphertext>& out);
+    void EvalFunc(const std::vector<LWECiphertext>& in, const std::vector<NativeInteger>& lut, const NativeInteger& beta,
+                  std::vector<LWECiphertext>& out);
+
+private:
+    void check(int rc, const char* what) const;
+    void flatten_bsk(const RingGSWACCKeyImpl& ek, std::vector<uint64_t>& out) const;
+    void load_keys(const RingGSWACCKey& ek, const LWESwitchingKey& ks);
+    void ensure_bsk(const RingGSWACCKey& ek);
+    void ensure_ksk(const LWESwitchingKey& ks);
+
+    int device_;
+    luxb200_ctx* h_ = nullptr;
+    luxb200_params p_{};
+    uint32_t digitsG_ = 0, digitsR_ = 0, rows_ = 0;
+    std::shared_ptr<ILNativeParams> poly_params_;
+    const void* bound_bsk_ = nullptr;   // identity of the key objects currently resident on the device
+    const void* bound_ksk_ = nullptr;
+};
+
+// Registers a BackendB200 bound to cc with the reference's registry and makes it the default backend.
+// Returns the registered instance (owned by the registry).
+BackendB200* RegisterB200(BinFHEContext& cc, int device = 0);
+
+}  // namespace backend
+}  // namespace lux::fhe

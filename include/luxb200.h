@@ -104,12 +104,24 @@ int luxb200_evalfunc_batch(luxb200_ctx* ctx, const uint64_t* a, const uint64_t* 
                            uint64_t lutlen, uint64_t beta, uint64_t* oa, uint64_t* ob, uint64_t count, uint64_t ctmod);
 /* a [count][n] mod amod; acc [count][2][N] EVALUATION format, in place */
 int luxb200_blind_rotate_batch(luxb200_ctx* ctx, const uint64_t* a, uint64_t amod, uint64_t* acc, uint64_t count);
+/* backend::Backend::ExternalProductBatch (backend.h:185-194): RGSW x RLWE -> RLWE as one AddToAccDM step computes it
+ * (rgsw-acc-dm.cpp:118-143).  rgsw [count][rows][2][N] (RingGSWEvalKeyImpl::GetElements order), rlwe / out [count][2][N];
+ * EVALUATION format, residues mod Q */
+int luxb200_external_product_batch(luxb200_ctx* ctx, const uint64_t* rgsw, const uint64_t* rlwe, uint64_t* out,
+                                   uint64_t count);
 /* a [count][N] mod qKS, b [count]  ->  oa [count][n], ob [count] mod qKS */
 int luxb200_keyswitch_batch(luxb200_ctx* ctx, const uint64_t* a, const uint64_t* b, uint64_t* oa, uint64_t* ob,
                             uint64_t count);
 /* elementwise RoundqQ (lwe-pke.cpp:41-46) over len values */
 int luxb200_modswitch_batch(luxb200_ctx* ctx, uint64_t qto, uint64_t qfrom, const uint64_t* in, uint64_t* out,
                             uint64_t len);
+
+/* ---- raw device memory: backend::Backend::Allocate / Free / CopyToDevice / CopyToHost / DeviceMemory
+ * (backend.h:88-113).  kind: 1 host->device, 2 device->host, 3 device->device */
+int luxb200_dev_alloc(int device, uint64_t bytes, void** out);
+int luxb200_dev_free(int device, void* ptr);
+int luxb200_dev_copy(int device, void* dst, const void* src, uint64_t bytes, int kind);
+int luxb200_dev_mem_info(int device, uint64_t* free_bytes, uint64_t* total_bytes);
 
 /* ---- NTT (context-free plan objects) ----------------------------------------------------------------- */
 typedef struct luxb200_ntt_plan luxb200_ntt_plan;

@@ -238,3 +238,47 @@ def test_ntt_full_size_linearity():
     ref = a[:64].copy(); O.orc_ntt(Q, O.orc_root_of_unity(2 * N, Q), N, P(ref), 64, 0, 8)
     assert (A[:64] == ref).all()
     pl.close()
+
+
+@pytest.mark.parametrize("name,method,cnt", [("TOY", "AP", 7), ("STD128", "GINX", 13)])
+def test_external_product_and_device_memory(name, method, cnt):
+    """Backend::ExternalProductBatch vs the oracle's primitives (INTT, SignedDigitDecompose, NTT, pointwise MAC:
+    rgsw-acc-dm.cpp:118-143), and Backend::Allocate/CopyToDevice/CopyToHost/Free round trip."""
+    import ctypes as C
+    from fhe_b200 import lib as _l
+    from fhe_b200.context import BinFHEContext
+    ctx = BinFHEContext().GenerateBinFHEContext(name, method)
+    oc = oracle_twin(ctx, method)
+    O = oracle()
+    N, Q, rows = ctx.N, ctx.Q, ctx.rows
+    rng = np.random.default_rng(5)
+    rgsw = rng.integers(0, Q, size=(cnt, rows, 2, N), dtype=np.uint64)
+    rlwe = rng.integers(0, Q, size=(cnt, 2, N), dtype=np.uint64)
+    rlwe[0] = Q - 1
+    rgsw[0] = Q - 1
+    got = ctx.ExternalProductBatch(rgsw, rlwe)
+    for i in range(cnt):
+        coef = rlwe[i].copy()
+        O.orc_ntt(Q, ctx.psi, N, P(coef), 2, 1, 1)
+        dct = np.zeros((rows, N), np.uint64)
+        O.orc_decompose(oc.h, P(coef), P(dct))
+        O.orc_ntt(Q, ctx.psi, N, P(dct), rows, 0, 1)
+        for c in range(2):
+            acc = np.zeros(N, np.uint64)
+            for l in range(rows):
+                acc = (acc + (dct[l] * rgsw[i, l, c]) % np.uint64(Q)) % np.uint64(Q)
+            assert (got[i, c] == acc).all(), (i, c)
+    # raw device memory
+    L = _l.load()
+    h = _l.VP()
+    buf = rng.integers(0, 2**63, size=4099, dtype=np.uint64)
+    back = np.zeros_like(buf)
+    _l.check(L.luxb200_dev_alloc(0, buf.nbytes, C.byref(h)))
+    _l.check(L.luxb200_dev_copy(0, h, _l.ptr(buf), buf.nbytes, 1))
+    _l.check(L.luxb200_dev_copy(0, _l.ptr(back), h, buf.nbytes, 2))
+    _l.check(L.luxb200_dev_free(0, h))
+    assert (back == buf).all()
+    f, t = _l.U64(0), _l.U64(0)
+    _l.check(L.luxb200_dev_mem_info(0, C.byref(f), C.byref(t)))
+    assert t.value > 100e9 and f.value <= t.value
+    ctx.close(); oc.close()

@@ -1,0 +1,51 @@
+"""C++ host layer (host/): BackendB200 + the batch API bodies, compiled against the reference's own headers.
+CPU: the library exports the reference's batch-API and backend symbols.  GPU: host/_build/host_parity drives the real
+reference (keygen, encrypt, CPU results) and compares every output of the host layer with it, bit for bit."""
+import json
+import os
+import subprocess
+
+import pytest
+
+from conftest import ROOT
+
+BUILD = os.path.join(ROOT, "host", "_build")
+LIB = os.path.join(BUILD, "libluxb200_host.so")
+BIN = os.path.join(BUILD, "host_parity")
+
+needs_build = pytest.mark.skipif(not os.path.exists(LIB), reason="host/_build not built (needs /root/reference headers: make -C host)")
+
+
+@needs_build
+def test_host_library_exports_reference_api():
+    out = subprocess.run(["nm", "-DC", "--defined-only", LIB], capture_output=True, text=True, check=True).stdout
+    for sym in ["lux::fhe::EvalBinGateBatch(", "lux::fhe::BootstrapBatch(", "lux::fhe::EvalFuncBatch(",
+                "lux::fhe::EvalFuncMultiOutputBatch(", "lux::fhe::EvalCMUXBatch(", "lux::fhe::KeySwitchBatch(",
+                "lux::fhe::ModSwitchBatch(", "lux::fhe::BootstrapBatchAsync(", "lux::fhe::BatchDAG::Execute(",
+                "lux::fhe::backend::BackendB200::BlindRotateBatch(", "lux::fhe::backend::BackendB200::ExternalProductBatch(",
+                "lux::fhe::backend::BackendB200::KeySwitchBatch(", "lux::fhe::backend::BackendB200::ModSwitchBatch(",
+                "lux::fhe::backend::BackendB200::PackBootstrappingKey(", "lux::fhe::backend::RegisterB200("]:
+        assert sym in out, sym
+
+
+@needs_build
+def test_host_layer_refuses_without_gpu():
+    from conftest import has_gpu
+    if has_gpu():
+        pytest.skip("GPU present")
+    r = subprocess.run([BIN, "TOY", "2", "0"], capture_output=True, text=True)
+    assert r.returncode != 0 and "no CPU fallback" in (r.stderr + r.stdout)
+
+
+@pytest.mark.gpu
+@needs_build
+@pytest.mark.parametrize("pset,cnt,pairs", [("TOY", 12, 2), ("TOY_AP", 12, 1), ("TOY_LMKCDEY", 12, 1), ("STD128", 9, 2),
+                                            ("STD128_LMKCDEY", 6, 1)])
+def test_host_layer_matches_reference(pset, cnt, pairs):
+    r = subprocess.run([BIN, pset, str(cnt), str(pairs)], capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    res = json.loads(r.stdout.strip().splitlines()[-1])
+    assert res["failed_checks"] == 0
+    for k in ["BootstrapBatch", "EvalCMUXBatch", "BatchDAG_levels", "GreaterThan8_circuit", "Backend_BlindRotateBatch",
+              "Backend_ExternalProductBatch", "Backend_KeySwitchBatch", "Backend_ModSwitchBatch", "Backend_PackUnpackBSK"]:
+        assert res[k] is True, k
