@@ -51,26 +51,49 @@ struct WNtt {
     }
     static constexpr int NB = offB(1) + E / 2;  // phase-B twiddles per lane
 
-    // bank-conflict-free swizzle for the A<->B transpose
+    // ---- A <-> B transpose through a per-warp N-word scratch ------------------------------------------------------
+    // The scratch is organised by layout-B rows (lane l owns words E*l .. E*l+E-1 = E/4 16-byte chunks); chunk v of row
+    // l is stored at chunk v ^ SB(l).  The layout-B side then moves whole chunks (STS.128 / LDS.128, conflict-free
+    // because 8 consecutive lanes get 8 different bank groups), and on the layout-A side index lane + 32r lives at word
+    // 32r + (lane ^ 4*SA(r)): a permutation of one 128-byte line per r, so it is conflict-free too and its address is
+    // one of at most 8 precomputed per-lane pointers plus the immediate 128*r — no per-access address arithmetic.
+    // (tools/mix_probe.cu: the scalar-both-sides transpose cost 25 % of the IMAD pipe, this one 12 %.)
+    static constexpr int NSW = (E >= 32) ? 8 : (E == 16) ? 4 : 2;                 // distinct swizzle values
+    __host__ __device__ static constexpr int SA(int r) { return (E >= 64) ? ((r >> 1) & 7) : (r & (NSW - 1)); }
+    __device__ static __forceinline__ u32 SB(u32 l) { return (E >= 32) ? (l & 7u) : (E == 16) ? ((l >> 1) & 3u) : ((l >> 2) & 1u); }
+    // word address of index j (generic; used by gathers such as the EVALUATION-format automorphism)
     __device__ static __forceinline__ u32 phys(u32 j) {
-        u32 f = (E >= 32) ? ((j >> LOGE) & 31u) : ((j >> 5) & 31u);
-        return j ^ f;
+        const u32 l = j >> LOGE, rr = j & (E - 1);
+        return (l << LOGE) + ((((rr >> 2) ^ SB(l)) << 2) | (rr & 3u));
     }
     __device__ static __forceinline__ void store_A(u32* sm, const u32 (&x)[E], int lane) {
+        u32* pk[NSW];
 #pragma unroll
-        for (int r = 0; r < E; ++r) sm[phys(lane + 32 * r)] = x[r];
+        for (int k = 0; k < NSW; ++k) pk[k] = sm + (lane ^ (4 * k));
+#pragma unroll
+        for (int r = 0; r < E; ++r) pk[SA(r)][32 * r] = x[r];
     }
     __device__ static __forceinline__ void load_A(const u32* sm, u32 (&x)[E], int lane) {
+        const u32* pk[NSW];
 #pragma unroll
-        for (int r = 0; r < E; ++r) x[r] = sm[phys(lane + 32 * r)];
+        for (int k = 0; k < NSW; ++k) pk[k] = sm + (lane ^ (4 * k));
+#pragma unroll
+        for (int r = 0; r < E; ++r) x[r] = pk[SA(r)][32 * r];
     }
     __device__ static __forceinline__ void store_B(u32* sm, const u32 (&x)[E], int lane) {
+        uint4* row   = reinterpret_cast<uint4*>(sm + E * lane);
+        const u32 sb = SB((u32)lane);
 #pragma unroll
-        for (int r = 0; r < E; ++r) sm[phys(E * lane + r)] = x[r];
+        for (int v = 0; v < E / 4; ++v) row[v ^ sb] = make_uint4(x[4 * v], x[4 * v + 1], x[4 * v + 2], x[4 * v + 3]);
     }
     __device__ static __forceinline__ void load_B(const u32* sm, u32 (&x)[E], int lane) {
+        const uint4* row = reinterpret_cast<const uint4*>(sm + E * lane);
+        const u32 sb     = SB((u32)lane);
 #pragma unroll
-        for (int r = 0; r < E; ++r) x[r] = sm[phys(E * lane + r)];
+        for (int v = 0; v < E / 4; ++v) {
+            const uint4 t = row[v ^ sb];
+            x[4 * v] = t.x; x[4 * v + 1] = t.y; x[4 * v + 2] = t.z; x[4 * v + 3] = t.w;
+        }
     }
 
     __device__ static __forceinline__ void ct(u32& a, u32& b, u32 w, u32 ws, u32 Q, u32 Q2) {
