@@ -30,7 +30,9 @@ PARAM_SETS = {
     "STD128Q": (25, 2048, 534, 1024, 16384, 32, 128, 32, 10, 0),
     "STD128_LMKCDEY": (28, 2048, 447, 2048, 16384, 32, 1024, 64, 10, 1),
     "STD128_3_LMKCDEY": (27, 2048, 556, 2048, 32768, 32, 512, 64, 10, 0),
+    "STD128_4_LMKCDEY": (27, 2048, 595, 2048, 65536, 64, 128, 64, 10, 0),
     "STD128Q_LMKCDEY": (27, 2048, 483, 2048, 16384, 32, 512, 64, 10, 1),
+    "STD128Q_3_LMKCDEY": (25, 2048, 643, 2048, 65536, 64, 128, 64, 10, 0),
     "LPF_STD128": (27, 2048, 556, 2048, 32768, 32, 128, 64, 10, 0),
     "LPF_STD128_LMKCDEY": (27, 2048, 556, 2048, 32768, 32, 512, 64, 10, 0),
     "SIGNED_MOD_TEST": (28, 2048, 512, 1024, PRIME, 25, 128, 23, 10, 0),

@@ -82,6 +82,10 @@ int main(int argc, char** argv) {
     else if (set == "STD128_LMKCDEY") { ps = STD128_LMKCDEY; method = LMKCDEY; }
     else if (set == "TOY_AP") { ps = TOY; method = AP; }
     else if (set == "TOY_LMKCDEY") { ps = TOY; method = LMKCDEY; }
+    else if (set == "MEDIUM") ps = MEDIUM;
+    else if (set == "STD128_3") ps = STD128_3;          // baseG = 128: digitsG - 1 = 3
+    else if (set == "STD128Q") ps = STD128Q;
+    else if (set == "STD128_4_LMKCDEY") { ps = STD128_4_LMKCDEY; method = LMKCDEY; }
 
     BinFHEContext cc;
     cc.GenerateBinFHEContext(ps, method);

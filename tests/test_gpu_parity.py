@@ -126,7 +126,12 @@ def _seeded_inputs(oc, sk, cnt, base):
 
 
 @pytest.mark.parametrize("name,method,cnt", [("TOY", "GINX", 33), ("TOY", "AP", 9), ("TOY", "LMKCDEY", 9),
-                                             ("STD128", "GINX", 6), ("STD128_LMKCDEY", "LMKCDEY", 4)])
+                                             ("STD128", "GINX", 6), ("STD128_LMKCDEY", "LMKCDEY", 4),
+                                             # the other N=1024 sets of binfhecontext.cpp:117-144, incl. baseG=128 (digitsG-1 = 3)
+                                             ("MEDIUM", "GINX", 3), ("STD128_3", "GINX", 3), ("STD128_4", "GINX", 3),
+                                             ("STD128Q", "GINX", 3), ("STD128_3_LMKCDEY", "LMKCDEY", 3),
+                                             ("STD128_4_LMKCDEY", "LMKCDEY", 3), ("STD128Q_3_LMKCDEY", "LMKCDEY", 3),
+                                             ("STD128Q_LMKCDEY", "LMKCDEY", 3)])
 def test_gates_vs_oracle(name, method, cnt):
     from fhe_b200.context import BinFHEContext
     ctx = BinFHEContext().GenerateBinFHEContext(name, method)

@@ -40,7 +40,7 @@ def test_host_layer_refuses_without_gpu():
 @pytest.mark.gpu
 @needs_build
 @pytest.mark.parametrize("pset,cnt,pairs", [("TOY", 12, 2), ("TOY_AP", 12, 1), ("TOY_LMKCDEY", 12, 1), ("STD128", 9, 2),
-                                            ("STD128_LMKCDEY", 6, 1)])
+                                            ("STD128_LMKCDEY", 6, 1), ("STD128_3", 6, 1), ("STD128_4_LMKCDEY", 6, 1)])
 def test_host_layer_matches_reference(pset, cnt, pairs):
     r = subprocess.run([BIN, pset, str(cnt), str(pairs)], capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
