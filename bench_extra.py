@@ -113,8 +113,75 @@ def method_gates(name, method, G, fn="gate"):
     return out
 
 
+def compare8(name, method, pairs):
+    """BASELINE configs[3]: the 8-bit GreaterThan8 circuit of go/tfhe/compare.go:106-139 over `pairs` independent
+    comparisons, level-batched on the device: one batch of 24*pairs carry-independent gates (a AND NOT b, NOT a AND b,
+    a XNOR b per bit), then 3 dependent levels per bit (24 batches of `pairs` gates); 48 bootstrapped gates per
+    comparison.  Ciphertexts stay in HBM as uint32; EvalNOT (binfhe-base-scheme.cpp:222-237) is the linear map
+    a -> -a, b -> q/4 - b.  Bit-exactness of this circuit against the reference is checked by host/host_parity.cpp;
+    here the result is decrypted and compared with the same circuit on the plaintext bits."""
+    ctx = BinFHEContext().GenerateBinFHEContext(name, method)
+    ks = kg.keygen(ctx, seed=31)
+    ctx.BTKeyLoad(ks.bsk, ks.kskA, ks.kskB)
+    rng = np.random.default_rng(8)
+    q, n = ctx.q, ctx.n
+    va = rng.integers(0, 256, pairs); vb = np.where(rng.integers(0, 2, pairs) == 1, rng.integers(0, 256, pairs), va ^ (1 << rng.integers(0, 8, pairs)))
+    bits_a = ((va[:, None] >> np.arange(8)) & 1).reshape(-1)          # [pairs*8], index p*8 + i
+    bits_b = ((vb[:, None] >> np.arange(8)) & 1).reshape(-1)
+
+    def dev(m):
+        a, b = kg.encrypt(ctx, ks.sk, m, rng)
+        return (torch.from_numpy(a.astype(np.uint32).view(np.int32)).cuda(), torch.from_numpy(b.astype(np.uint32).view(np.int32)).cuda())
+
+    def NOT(ct):
+        a, b = ct
+        return (torch.where(a == 0, a, q - a), torch.remainder(q // 4 - b, q))
+
+    def gate(g, x, y):
+        cnt = x[1].numel()
+        oa = torch.empty((cnt, n), dtype=torch.int32, device="cuda"); ob = torch.empty(cnt, dtype=torch.int32, device="cuda")
+        xa, xb, ya, yb = x[0].contiguous(), x[1].contiguous(), y[0].contiguous(), y[1].contiguous()
+        ctx.EvalBinGateBatchDev(g, xa.data_ptr(), xb.data_ptr(), ya.data_ptr(), yb.data_ptr(), oa.data_ptr(), ob.data_ptr(), cnt)
+        ctx.Synchronize()   # inputs of this level are temporaries
+        return (oa, ob)
+
+    A, B, init = dev(bits_a), dev(bits_b), dev(np.zeros(pairs, np.int64))
+
+    def circuit():
+        aG, bG, eq = gate("AND", A, NOT(B)), gate("AND", NOT(A), B), gate("XNOR", A, B)
+        res = init
+        for i in range(7, -1, -1):
+            sel = torch.arange(pairs, device="cuda") * 8 + i
+            e, g, nb = (eq[0][sel], eq[1][sel]), (aG[0][sel], aG[1][sel]), NOT((bG[0][sel], bG[1][sel]))
+            res = gate("AND", e, res)
+            res = gate("OR", g, res)
+            res = gate("AND", res, nb)
+        return res
+
+    circuit()   # warm-up
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    res = circuit()
+    torch.cuda.synchronize()
+    dt = time.perf_counter() - t0
+    oa = res[0].cpu().numpy().view(np.uint32).astype(np.uint64); ob = res[1].cpu().numpy().view(np.uint32).astype(np.uint64)
+    dec = kg.decrypt(ctx, ks.sk, oa, ob)
+    exp = np.zeros(pairs, np.int64)
+    for p in range(pairs):
+        r = 0
+        for i in range(7, -1, -1):
+            ai, bi = (int(va[p]) >> i) & 1, (int(vb[p]) >> i) & 1
+            r = (ai & (1 - bi)) | (int(ai == bi) & r)
+            r = r & (1 - ((1 - ai) & bi))
+        exp[p] = r
+    ctx.close()
+    return {"workload": f"{name}/{method} GreaterThan8 circuit x{pairs} (48 gates each, 25 batched levels)",
+            "comparisons_per_s": pairs / dt, "bootstraps_per_s": 48 * pairs / dt, "seconds": dt,
+            "decrypt_errors": int((dec != exp).sum())}
+
+
 if __name__ == "__main__":
-    which = sys.argv[1:] or ["ntt32", "ntt64", "methods"]
+    which = sys.argv[1:] or ["ntt32", "ntt64", "methods", "compare"]
     if "ntt32" in which:
         print(json.dumps(ntt32(1024, 27, 65536)))
         print(json.dumps(ntt32(2048, 29, 65536)))
@@ -122,6 +189,9 @@ if __name__ == "__main__":
         print(json.dumps(ntt64(65536, 32, 64)))
         print(json.dumps(ntt64(16384, 16, 64)))
         print(json.dumps(ntt64(4096, 8, 512)))
+    if "compare" in which:
+        print(json.dumps(compare8("STD128", "GINX", 4096)))
+        print(json.dumps(compare8("STD128_LMKCDEY", "LMKCDEY", 4096)))
     if "methods" in which:
         print(json.dumps(method_gates("STD128_LMKCDEY", "LMKCDEY", 16384)))
         print(json.dumps(method_gates("STD128_AP", "AP", 4096)))
