@@ -49,3 +49,31 @@ def test_host_layer_matches_reference(pset, cnt, pairs):
     for k in ["BootstrapBatch", "EvalCMUXBatch", "BatchDAG_levels", "GreaterThan8_circuit", "Backend_BlindRotateBatch",
               "Backend_ExternalProductBatch", "Backend_KeySwitchBatch", "Backend_ModSwitchBatch", "Backend_PackUnpackBSK"]:
         assert res[k] is True, k
+
+
+CAPI = os.path.join(BUILD, "c_api_parity")
+
+
+@needs_build
+def test_c_abi_batch_symbols_and_refusal():
+    """include/lux/fhe/c_api_batch.h: every declared symbol is exported next to the reference's own lux_fhe_* calls, and
+    without a CUDA device lux_fhe_gpu_enable fails (the batch calls never run the CPU loop)."""
+    out = subprocess.run(["nm", "-D", "--defined-only", LIB], capture_output=True, text=True, check=True).stdout
+    for sym in ["lux_fhe_gpu_enable", "lux_fhe_mux_batch", "lux_fhe_bootstrap_batch", "lux_fhe_and", "lux_fhe_context_new"] + \
+               [f"lux_fhe_{g}_batch" for g in ("and", "or", "xor", "nand", "nor", "xnor")]:
+        assert f" T {sym}\n" in out, sym
+    from conftest import has_gpu
+    if not has_gpu():
+        r = subprocess.run([CAPI, "toy", "2"], capture_output=True, text=True, timeout=600)
+        assert r.returncode == 3 and "no CPU fallback" in r.stdout
+
+
+@pytest.mark.gpu
+@needs_build
+@pytest.mark.parametrize("pset,cnt", [("toy", 8), ("std128", 8)])
+def test_c_abi_batch_matches_single_calls(pset, cnt):
+    """plain-C program over the FFI: lux_fhe_<gate>_batch / mux_batch / bootstrap_batch (B200) vs the reference's
+    lux_fhe_<gate> / mux / bootstrap (CPU), compared through lux_fhe_ciphertext_marshal bytes."""
+    r = subprocess.run([CAPI, pset, str(cnt)], capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    assert json.loads(r.stdout.strip().splitlines()[-1])["failed_checks"] == 0
