@@ -1,5 +1,6 @@
 // backend_b200.cpp — see backend_b200.h.  Pack -> one luxb200_* call -> unpack; no arithmetic here.
 #include "backend_b200.h"
+#include "packed_b200.h"
 
 #include <cstring>
 #include <stdexcept>
@@ -272,6 +273,59 @@ void BackendB200::ModSwitch(const std::shared_ptr<LWECryptoParams>& params, cons
 }
 
 // ---- packed formats (backend.h:213-246) -----------------------------------------------------------------------
+// Packed wire bytes (backend/packed.h formats, host/packed_b200.cpp) -> canonical flat arrays -> device, without
+// rebuilding the RingGSWACCKey / LWESwitchingKey object graphs.
+void BackendB200::LoadPacked(const uint8_t* bsk, size_t bsk_size, const uint8_t* ksk, size_t ksk_size) {
+    if (!h_) throw std::runtime_error("BackendB200::LoadPacked: Bind() first");
+    if (bsk) {
+        PackedBSKView v;
+        if (!ParsePackedBSK(bsk, bsk_size, v)) throw std::invalid_argument("BackendB200::LoadPacked: invalid packed bootstrapping key");
+        if (v.head->rlwe_N != p_.N || v.layout->Q != p_.Q || v.layout->method != p_.method || v.head->lwe_n != p_.n)
+            throw std::invalid_argument("BackendB200::LoadPacked: packed bootstrapping key does not match the bound parameter set");
+        const uint32_t d1 = v.layout->dims[1], d2 = v.layout->dims[2];
+        std::vector<size_t> off(v.slots + 1, 0);   // coefficient offset of every slot
+        for (size_t s = 0; s < v.slots; ++s) off[s + 1] = off[s] + size_t(v.rows[s]) * 2 * p_.N;
+        std::vector<uint64_t> flat(luxb200_bsk_len(h_), 0);
+        size_t pos = 0;
+        auto put = [&](uint32_t i, uint32_t j, uint32_t k, uint32_t want_rows) {
+            const size_t s = (size_t(i) * d1 + j) * d2 + k;
+            if (i >= v.layout->dims[0] || j >= d1 || k >= d2 || v.rows[s] != want_rows || pos + off[s + 1] - off[s] > flat.size())
+                throw std::invalid_argument("BackendB200::LoadPacked: packed bootstrapping key has the wrong shape for this method");
+            for (size_t t = off[s]; t < off[s + 1]; ++t) flat[pos++] = v.coeff(t);
+        };
+        switch (p_.method) {
+            case LUXB200_GINX:
+                for (uint32_t i = 0; i < p_.n; ++i) { put(0, 0, i, rows_); put(0, 1, i, rows_); }
+                break;
+            case LUXB200_AP:
+                for (uint32_t i = 0; i < p_.n; ++i)
+                    for (uint32_t j = 0; j < p_.baseR; ++j)
+                        for (uint32_t k = 0; k < digitsR_; ++k) {
+                            if (j == 0) pos += size_t(rows_) * 2 * p_.N;
+                            else put(i, j, k, rows_);
+                        }
+                break;
+            default:
+                for (uint32_t i = 0; i < p_.n; ++i) put(0, 0, i, rows_);
+                for (uint32_t t = 0; t <= p_.numAutoKeys; ++t) put(0, 1, t, digitsG_ - 1);
+        }
+        if (pos != flat.size()) throw std::invalid_argument("BackendB200::LoadPacked: packed bootstrapping key is incomplete");
+        check(luxb200_load_bsk(h_, flat.data(), 0), "load_bsk");
+        bound_bsk_ = bsk;
+    }
+    if (ksk) {
+        PackedKSKView v;
+        if (!ParsePackedKSK(ksk, ksk_size, v)) throw std::invalid_argument("BackendB200::LoadPacked: invalid packed switching key");
+        std::vector<uint64_t> A(luxb200_ksk_len(h_)), B(A.size() / p_.n);
+        if (v.head->input_n != p_.N || v.head->output_n != p_.n || v.head->Q != p_.qKS || v.base != p_.baseKS || v.vecs != B.size())
+            throw std::invalid_argument("BackendB200::LoadPacked: packed switching key does not match the bound parameter set");
+        for (size_t t = 0; t < A.size(); ++t) A[t] = v.coeff(v.A, t);
+        for (size_t t = 0; t < B.size(); ++t) B[t] = v.coeff(v.B, t);
+        check(luxb200_load_ksk(h_, A.data(), B.data(), 0), "load_ksk");
+        bound_ksk_ = ksk;
+    }
+}
+
 DeviceBuffer BackendB200::PackBootstrappingKey(const RingGSWACCKey& ek) {
     if (!ek) throw std::invalid_argument("BackendB200::PackBootstrappingKey: empty key");
     std::vector<uint64_t> flat;

@@ -66,6 +66,10 @@ public:
     DeviceBuffer PackCiphertexts(const std::vector<LWECiphertext>& cts) override;     // [count][n+1]: a then b
     void UnpackCiphertexts(const DeviceBuffer& packed, std::vector<LWECiphertext>& cts) override;
 
+    // Keys from the packed wire formats of backend/packed.h (PackBootstrappingKey / PackSwitchingKey bytes, see
+    // host/packed_b200.cpp) straight to the device; either pointer may be null.  Requires Bind() (parameters) first.
+    void LoadPacked(const uint8_t* bsk, size_t bsk_size, const uint8_t* ksk, size_t ksk_size);
+
     // Gate-level entry points used by the batch API bodies (host/batch_b200.cpp)
     void EvalBinGate(BINGATE gate, const std::vector<LWECiphertext>& ct1, const std::vector<LWECiphertext>& ct2,
                      std::vector<LWECiphertext>& out);

@@ -77,3 +77,28 @@ def test_c_abi_batch_matches_single_calls(pset, cnt):
     r = subprocess.run([CAPI, pset, str(cnt)], capture_output=True, text=True, timeout=900)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
     assert json.loads(r.stdout.strip().splitlines()[-1])["failed_checks"] == 0
+
+
+PACKED = os.path.join(BUILD, "packed_parity")
+
+
+@needs_build
+@pytest.mark.parametrize("pset", ["TOY", "TOY_AP", "TOY_LMKCDEY"])
+def test_packed_key_formats_roundtrip_cpu(pset):
+    """backend/packed.h key formats (host/packed_b200.cpp; the reference leaves them empty, packed.cpp:284-331): reference
+    keygen -> Pack -> Unpack gives identical keys, malformed bytes are refused, and the reference's CPU gate on the
+    unpacked keys equals the gate on the original keys.  No GPU involved."""
+    r = subprocess.run([PACKED, pset, "4", "0"], capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    assert json.loads(r.stdout.strip().splitlines()[-1])["failed_checks"] == 0
+
+
+@pytest.mark.gpu
+@needs_build
+@pytest.mark.parametrize("pset,cnt", [("TOY", 16), ("TOY_AP", 8), ("TOY_LMKCDEY", 8), ("STD128", 8), ("STD128_LMKCDEY", 6)])
+def test_packed_keys_load_on_b200(pset, cnt):
+    """a context that never held keys: BackendB200::LoadPacked(bytes) then EvalBinGateBatch == reference CPU gates."""
+    r = subprocess.run([PACKED, pset, str(cnt), "1"], capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    assert "B200 gates on LoadPacked keys == reference" in r.stdout
+    assert json.loads(r.stdout.strip().splitlines()[-1])["failed_checks"] == 0
