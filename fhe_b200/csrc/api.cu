@@ -44,6 +44,7 @@ int Ntt32Tables::build(uint32_t N_, uint64_t Q_, uint64_t psi_) {
         C.twiA[i] = make_uint2((u32)twi[i], shoup32(twi[i], Q));
     }
     C.Q = (u32)Q; C.Q2 = (u32)(2 * Q); C.mu32 = (u32)((1ull << 32) / Q);
+    for (int k = 0; k < 8; ++k) C.QM[k] = (u32)(Q << k);   // only multiples below 2^32 are ever used (bounds <= 2^LOGH)
     uint64_t ninv = invmod_prime(N % Q, Q);
     C.ninv = (u32)ninv; C.ninv_s = shoup32(ninv, Q);
     uint64_t w1 = mulmod(twi[1], ninv, Q);

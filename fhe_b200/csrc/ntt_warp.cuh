@@ -23,15 +23,18 @@ struct NttConsts {
     u32 ninv, ninv_s;      // N^-1 and its Shoup companion
     u32 w1ninv, w1ninv_s;  // TableI[1] * N^-1 (transformnat-impl.h:537-538)
     u32 pad;
+    u32 QM[8];             // Q << k: read as constant-bank operands (IADD3 / VIADDMNMX take c[][] directly), so the lazy
+                           // offsets cost no IMAD/LEA to rematerialise and no register to keep
 };
+__host__ __device__ constexpr int ntt_ilog2(int v) { return v <= 1 ? 0 : 1 + ntt_ilog2(v >> 1); }
 
 // x < bound*Q -> [0, 2Q) by a ladder of conditional subtractions (VIADDMNMX on the ALU pipe) instead of a Barrett
 // step (IMAD.HI + IMAD on the IMAD pipe, which is the pipe these kernels saturate: ncu r1, fmaheavy 69 %).
 // `bound` is a compile-time constant after unrolling, so the ladder folds to ceil(log2(bound)) - 1 instructions.
-__device__ __forceinline__ u32 ladder_2q(u32 x, int bound, u32 Q2) {
+__device__ __forceinline__ u32 ladder_2q(u32 x, int bound, const NttConsts& C) {
 #pragma unroll
     for (int k = 4; k >= 0; --k)
-        if ((2 << k) < bound) x = csub(x, Q2 << k);
+        if ((2 << k) < bound) x = csub(x, C.QM[k + 1]);
     return x;
 }
 
@@ -114,7 +117,7 @@ struct WNtt {
         for (int s = LOGE - 1; s >= 0; --s) {  // in-register stride tr = 2^s  (global half-size t = 32 tr)
             if (bound + 2 > H) {
 #pragma unroll
-                for (int r = 0; r < E; ++r) x[r] = ladder_2q(x[r], bound, Q2);
+                for (int r = 0; r < E; ++r) x[r] = ladder_2q(x[r], bound, C);
                 bound = 2;
             }
 #pragma unroll
@@ -130,7 +133,7 @@ struct WNtt {
             for (int t = 16; t >= E; t >>= 1) {
                 if (bound + 2 > H) {
 #pragma unroll
-                    for (int r = 0; r < E; ++r) x[r] = ladder_2q(x[r], bound, Q2);
+                    for (int r = 0; r < E; ++r) x[r] = ladder_2q(x[r], bound, C);
                     bound = 2;
                 }
                 const bool hi = lane & t;
@@ -152,14 +155,14 @@ struct WNtt {
         for (int s = LOGTB; s >= 0; --s) {  // in-register stride t = 2^s
             if (bound + 2 > H) {
 #pragma unroll
-                for (int r = 0; r < E; ++r) x[r] = ladder_2q(x[r], bound, Q2);
+                for (int r = 0; r < E; ++r) x[r] = ladder_2q(x[r], bound, C);
                 bound = 2;
             }
             if (s == 0 && bound > 2) {
                 // last stage: bring only the sum operand to [0, 2Q); both results are then < 4Q, and the final
                 // conditional subtraction below makes them < 2Q (half as many ladders as reducing every output)
 #pragma unroll
-                for (int qq = 0; qq < E / 2; ++qq) x[2 * qq] = ladder_2q(x[2 * qq], bound, Q2);
+                for (int qq = 0; qq < E / 2; ++qq) x[2 * qq] = ladder_2q(x[2 * qq], bound, C);
                 bound = 2;
             }
 #pragma unroll
@@ -172,17 +175,17 @@ struct WNtt {
         }
         if (bound > 2) {
 #pragma unroll
-            for (int r = 0; r < E; ++r) x[r] = ladder_2q(x[r], bound, Q2);
+            for (int r = 0; r < E; ++r) x[r] = ladder_2q(x[r], bound, C);
         }
     }
 
     // ---- inverse: layout B in (values in [0, 2Q)), layout A out, canonical [0, Q) --------------------------
     // operands < bound*Q; the sum (< 2*bound*Q) is laddered down to [0, 2Q) when `red`
-    __device__ static __forceinline__ void gs(u32& a, u32& b, u32 w, u32 ws, u32 Q, int bound, bool red) {
-        u32 d = a - b + (u32)bound * Q;
+    __device__ static __forceinline__ void gs(u32& a, u32& b, u32 w, u32 ws, const NttConsts& C, int bound, bool red) {
+        u32 d = a - b + C.QM[ntt_ilog2(bound)];   // bound is a power of two
         a     = a + b;
-        if (red) a = ladder_2q(a, 2 * bound, 2 * Q);
-        b = shoup_mul(d, w, ws, Q);
+        if (red) a = ladder_2q(a, 2 * bound, C);
+        b = shoup_mul(d, w, ws, C.Q);
     }
     __device__ static __forceinline__ void inverse(u32 (&x)[E], const NttConsts& C, u32* sm, const uint2* twiB,
                                                    const uint2* __restrict__ twifull, int lane) {
@@ -195,7 +198,7 @@ struct WNtt {
             for (int qq = 0; qq < E / 2; ++qq) {
                 const int t = 1 << s, i = qq >> s, r = (i << (s + 1)) | (qq & (t - 1));
                 const uint2 w = twiB[(offB(t) + i) * 32 + lane];
-                gs(x[r], x[r + t], w.x, w.y, Q, bound, red);
+                gs(x[r], x[r + t], w.x, w.y, C, bound, red);
             }
             bound = red ? 2 : 2 * bound;
         }
@@ -213,8 +216,8 @@ struct WNtt {
                     const uint2 w = twifull[N / (2 * t) + (32 * r + lane) / (2 * t)];
                     u32 v         = __shfl_xor_sync(0xffffffffu, x[r], t);
                     u32 s         = x[r] + v;
-                    if (red) s = ladder_2q(s, 2 * bound, 2 * Q);
-                    u32 d = shoup_mul(v - x[r] + (u32)bound * Q, w.x, w.y, Q);
+                    if (red) s = ladder_2q(s, 2 * bound, C);
+                    u32 d = shoup_mul(v - x[r] + C.QM[ntt_ilog2(bound)], w.x, w.y, Q);
                     x[r]  = hi ? d : s;
                 }
                 bound = red ? 2 : 2 * bound;
@@ -227,13 +230,13 @@ struct WNtt {
             for (int qq = 0; qq < E / 2; ++qq) {
                 const int tr = 1 << s, i = qq >> s, r = (i << (s + 1)) | (qq & (tr - 1));
                 const uint2 w = C.twiA[(E >> (s + 1)) + i];
-                gs(x[r], x[r + tr], w.x, w.y, Q, bound, red);
+                gs(x[r], x[r + tr], w.x, w.y, C, bound, red);
             }
             bound = red ? 2 : 2 * bound;
         }
         // last stage (t = N/2) with N^-1 folded in; outputs canonical
         {
-            const u32 BQ = (u32)bound * Q;
+            const u32 BQ = C.QM[ntt_ilog2(bound)];
 #pragma unroll
             for (int r = 0; r < E / 2; ++r) {
                 u32 a = x[r], b = x[r + E / 2];
