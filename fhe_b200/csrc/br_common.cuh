@@ -53,7 +53,7 @@ __device__ __forceinline__ void decompose_coeff(u32 t, u32 Q, u32 qhalf, int gbi
     for (int k = 0; k < ND; ++k) {
         r0 = sext(d, gbits);
         d  = (d - r0) >> gbits;
-        out[k] = (r0 < 0) ? (u32)(r0 + (i32)Q) : (u32)r0;
+        out[k] = min((u32)r0, (u32)r0 + Q);   // r0 < 0 ? r0 + Q : r0 as one VIADDMNMX.U32 (a negative r0 is > r0 + Q unsigned)
     }
 }
 
