@@ -37,6 +37,14 @@ __device__ __forceinline__ u32 ladder_2q(u32 x, int bound, const NttConsts& C) {
         if ((2 << k) < bound) x = csub(x, C.QM[k + 1]);
     return x;
 }
+// x < from*Q -> x < to*Q (to a power of two): ceil(log2(from/to)) conditional subtractions
+__device__ __forceinline__ u32 ladder_to(u32 x, int from, int to, const NttConsts& C) {
+#pragma unroll
+    for (int k = 5; k >= 0; --k)
+        if ((to << k) < from) x = csub(x, C.QM[ntt_ilog2(to) + k]);
+    return x;
+}
+__host__ __device__ constexpr int ntt_clog2(int v) { return ntt_ilog2(v) + (((1 << ntt_ilog2(v)) < v) ? 1 : 0); }
 
 template <int LOGN, int LOGH>
 struct WNtt {
@@ -180,33 +188,48 @@ struct WNtt {
     }
 
     // ---- inverse: layout B in (values in [0, 2Q)), layout A out, canonical [0, Q) --------------------------
-    // operands < bound*Q; the sum (< 2*bound*Q) is laddered down to [0, 2Q) when `red`
-    __device__ static __forceinline__ void gs(u32& a, u32& b, u32 w, u32 ws, const NttConsts& C, int bound, bool red) {
-        u32 d = a - b + C.QM[ntt_ilog2(bound)];   // bound is a power of two
-        a     = a + b;
-        if (red) a = ladder_2q(a, 2 * bound, C);
-        b = shoup_mul(d, w, ws, C.Q);
+    // Gentleman-Sande: a' = a + b doubles the bound of the sum path, b' = (a - b + kQ) * w comes back < 2Q.  Bounds are
+    // tracked PER REGISTER at compile time: after j stages only the registers whose low j index bits are 0 carry the
+    // maximal bound, half of them are < 2Q, a quarter < 4Q, ... so only the few registers that would overflow are
+    // laddered (37 conditional subtractions per N=1024 transform at H = 32 instead of 128 with one bound per stage).
+    __device__ static __forceinline__ void gs_pair(u32& a, u32& b, int& ba, int& bb, u32 w, u32 ws, const NttConsts& C) {
+        if (ba + bb > H) {   // the sum must stay below H*Q < 2^32
+            a = ladder_to(a, ba, H / 2, C); ba = ba < H / 2 ? ba : H / 2;
+            b = ladder_to(b, bb, H / 2, C); bb = bb < H / 2 ? bb : H / 2;
+        }
+        const u32 d = a - b + C.QM[ntt_clog2(bb)];
+        a  = a + b;
+        ba = ba + bb;
+        b  = shoup_mul(d, w, ws, C.Q);
+        bb = 2;
     }
     __device__ static __forceinline__ void inverse(u32 (&x)[E], const NttConsts& C, u32* sm, const uint2* twiB,
                                                    const uint2* __restrict__ twifull, int lane) {
         const u32 Q = C.Q;
-        int bound   = 2;  // 2*bound <= H holds on entry to every stage
+        int bnd[E];
+#pragma unroll
+        for (int r = 0; r < E; ++r) bnd[r] = 2;
 #pragma unroll
         for (int s = 0; s <= LOGTB; ++s) {
-            const bool red = 4 * bound > H;
 #pragma unroll
             for (int qq = 0; qq < E / 2; ++qq) {
                 const int t = 1 << s, i = qq >> s, r = (i << (s + 1)) | (qq & (t - 1));
                 const uint2 w = twiB[(offB(t) + i) * 32 + lane];
-                gs(x[r], x[r + t], w.x, w.y, C, bound, red);
+                gs_pair(x[r], x[r + t], bnd[r], bnd[r + t], w.x, w.y, C);
             }
-            bound = red ? 2 : 2 * bound;
+        }
+        // after the transpose a register's history depends on the lane, so phase A starts from one bound: [0, 2Q)
+#pragma unroll
+        for (int r = 0; r < E; ++r) {
+            x[r]   = ladder_to(x[r], bnd[r], 2, C);
+            bnd[r] = 2;
         }
         __syncwarp();
         store_B(sm, x, lane);
         __syncwarp();
         load_A(sm, x, lane);
         if (E < 32) {
+            int bound = 2;
 #pragma unroll
             for (int t = E; t <= 16; t <<= 1) {
                 const bool red = 4 * bound > H;
@@ -222,26 +245,30 @@ struct WNtt {
                 }
                 bound = red ? 2 : 2 * bound;
             }
+#pragma unroll
+            for (int r = 0; r < E; ++r) bnd[r] = bound;
         }
 #pragma unroll
         for (int s = 0; s < LOGE - 1; ++s) {
-            const bool red = 4 * bound > H;
 #pragma unroll
             for (int qq = 0; qq < E / 2; ++qq) {
                 const int tr = 1 << s, i = qq >> s, r = (i << (s + 1)) | (qq & (tr - 1));
                 const uint2 w = C.twiA[(E >> (s + 1)) + i];
-                gs(x[r], x[r + tr], w.x, w.y, C, bound, red);
+                gs_pair(x[r], x[r + tr], bnd[r], bnd[r + tr], w.x, w.y, C);
             }
-            bound = red ? 2 : 2 * bound;
         }
         // last stage (t = N/2) with N^-1 folded in; outputs canonical
         {
-            const u32 BQ = C.QM[ntt_ilog2(bound)];
 #pragma unroll
             for (int r = 0; r < E / 2; ++r) {
                 u32 a = x[r], b = x[r + E / 2];
+                int ba = bnd[r], bb = bnd[r + E / 2];
+                if (ba + bb > H) {
+                    a = ladder_to(a, ba, H / 2, C); ba = ba < H / 2 ? ba : H / 2;
+                    b = ladder_to(b, bb, H / 2, C); bb = bb < H / 2 ? bb : H / 2;
+                }
                 x[r]         = csub(shoup_mul(a + b, C.ninv, C.ninv_s, Q), Q);
-                x[r + E / 2] = csub(shoup_mul(a - b + BQ, C.w1ninv, C.w1ninv_s, Q), Q);
+                x[r + E / 2] = csub(shoup_mul(a - b + C.QM[ntt_clog2(bb)], C.w1ninv, C.w1ninv_s, Q), Q);
             }
         }
     }
