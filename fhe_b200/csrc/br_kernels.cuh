@@ -2,6 +2,8 @@
 // (BootstrapGateCore / BootstrapFuncCore, binfhe-base-scheme.cpp:525-626) + extraction epilogue
 // (Transpose, INTT, b = acc1[0] + offset; binfhe-base-scheme.cpp:111-121, :634-639).
 #pragma once
+#include <type_traits>
+
 #include "br_common.cuh"
 
 enum { M_AP = 1, M_GINX = 2, M_LMKCDEY = 3 };
@@ -13,6 +15,15 @@ struct BrSmem {
     uint2 twiB[W::NB * 32];
     u32 scratch[2 * CTS][W::N];        // per-warp transpose scratch
     uint4 exch[CTS][ROWS][W::N / 4];   // NTT'd digit polynomials, sigma order, shared by the warp pair
+};
+// GINX with digitsG-1 = 2: every ciphertext of the CTA multiplies by the same key pair (ek+_i, ek-_i) in step i, and the
+// 64 KB pair fits beside the rest (224.5 of 227 KB), so one bulk async copy per step stages it while the transforms
+// run; the multiply-accumulate then reads keys with LDS.128 instead of waiting on L2 (ncu v4: long_scoreboard 5 %,
+// all of it on the IMAD.WIDE that consume the key loads).
+template <int LOGN, int LOGH, int ROWS, int CTS>
+struct GinxSmem : BrSmem<LOGN, LOGH, ROWS, CTS> {
+    uint4 keys[2][ROWS * 2][(1 << LOGN) / 4];   // [ek+ | ek-][row*2 + component][sigma(N)]
+    u64 mbar;
 };
 
 // ---- digit pipeline: INTT -> decompose -> NTT -> publish (rows 2k+c) -------------------------------------
@@ -50,7 +61,7 @@ __device__ __forceinline__ u32 comp4(const uint4& v, int e) {
 
 // ---- GINX accumulator update (rgsw-acc-cggi.cpp:132-150) -----------------------------------------------
 // acc[c] += (sum_row dct[row] * ek1[row][c]) * mono + (sum_row dct[row] * ek2[row][c]) * monoNeg
-template <int LOGN, int ROWS>
+template <int LOGN, int ROWS, bool SMEM_KEYS = false>
 __device__ __forceinline__ void mac_ginx(u32 (&acc)[(1 << LOGN) / 32], const u32 (&dg)[ROWS / 2][(1 << LOGN) / 32],
                                          const uint4* exch, const BrParams& P, const u32* ek1, const u32* ek2,
                                          const u32* mp, const u32* mn, int c, int lane) {
@@ -61,8 +72,13 @@ __device__ __forceinline__ void mac_ginx(u32 (&acc)[(1 << LOGN) / 32], const u32
         uint4 k1[ROWS], k2[ROWS], dx[ROWS / 2];
 #pragma unroll
         for (int row = 0; row < ROWS; ++row) {
-            k1[row] = __ldg(reinterpret_cast<const uint4*>(ek1 + (size_t)(row * 2 + c) * N) + v * 32 + lane);
-            k2[row] = __ldg(reinterpret_cast<const uint4*>(ek2 + (size_t)(row * 2 + c) * N) + v * 32 + lane);
+            if (SMEM_KEYS) {   // ek1 / ek2 point into shared memory (GinxSmem::keys)
+                k1[row] = (reinterpret_cast<const uint4*>(ek1) + (row * 2 + c) * (N / 4))[v * 32 + lane];
+                k2[row] = (reinterpret_cast<const uint4*>(ek2) + (row * 2 + c) * (N / 4))[v * 32 + lane];
+            } else {
+                k1[row] = __ldg(reinterpret_cast<const uint4*>(ek1 + (size_t)(row * 2 + c) * N) + v * 32 + lane);
+                k2[row] = __ldg(reinterpret_cast<const uint4*>(ek2 + (size_t)(row * 2 + c) * N) + v * 32 + lane);
+            }
         }
         const uint4 m1 = __ldg(reinterpret_cast<const uint4*>(mp) + v * 32 + lane);
         const uint4 m2 = __ldg(reinterpret_cast<const uint4*>(mn) + v * 32 + lane);
@@ -183,16 +199,23 @@ template <int LOGN, int LOGH, int ROWS, int CTS>
 __global__ void __launch_bounds__(64 * CTS, 1)
 br_ginx_kernel(const __grid_constant__ BrParams P) {
     using W         = WNtt<LOGN, LOGH>;
-    using S         = BrSmem<LOGN, LOGH, ROWS, CTS>;
+    constexpr bool STAGE = (ROWS == 4);   // see GinxSmem
+    using S         = typename std::conditional<STAGE, GinxSmem<LOGN, LOGH, ROWS, CTS>, BrSmem<LOGN, LOGH, ROWS, CTS>>::type;
     constexpr int N = W::N, E = W::E;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     S& sm = *reinterpret_cast<S*>(smem_raw);
+    GinxSmem<LOGN, LOGH, ROWS, CTS>& ks = *reinterpret_cast<GinxSmem<LOGN, LOGH, ROWS, CTS>*>(smem_raw);  // STAGE only
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int slot = warp >> 1, c = warp & 1;
     for (int i = threadIdx.x; i < W::NB * 32; i += blockDim.x) {
         sm.twB[i]  = P.twB[i];
         sm.twiB[i] = P.twiB[i];
+    }
+    constexpr u32 KEY_BYTES = 2u * ROWS * 2 * N * 4;   // ek+_i and ek-_i are adjacent in the device BSK
+    if (STAGE && threadIdx.x == 0) {
+        brtma::mbar_init(&ks.mbar, 1);
+        if (P.n) brtma::bulk_load(&ks.keys[0][0][0], P.bsk, KEY_BYTES, &ks.mbar);
     }
     __syncthreads();
     const u32 ct_raw = blockIdx.x * CTS + slot;
@@ -227,8 +250,18 @@ br_ginx_kernel(const __grid_constant__ BrParams P) {
         const u32* ek1 = P.bsk + (size_t)(2 * i) * kblock;
         const u32* mp  = P.mono + (size_t)ap * N;
         const u32* mn  = P.mono + (size_t)((2 * N - ap) & (2 * N - 1)) * N;
-        mac_ginx<LOGN, ROWS>(acc, dg, exch, P, ek1, ek1 + kblock, mp, mn, c, lane);
+        if (STAGE) {
+            brtma::mbar_wait(&ks.mbar, i & 1);
+            mac_ginx<LOGN, ROWS, true>(acc, dg, exch, P, reinterpret_cast<const u32*>(&ks.keys[0][0][0]),
+                                       reinterpret_cast<const u32*>(&ks.keys[1][0][0]), mp, mn, c, lane);
+        } else {
+            mac_ginx<LOGN, ROWS>(acc, dg, exch, P, ek1, ek1 + kblock, mp, mn, c, lane);
+        }
         __syncthreads();
+        if (STAGE && threadIdx.x == 0 && i + 1 < P.n) {   // every warp is past its key reads: refill for step i+1
+            brtma::fence_async();
+            brtma::bulk_load(&ks.keys[0][0][0], ek1 + 2 * kblock, KEY_BYTES, &ks.mbar);
+        }
     }
     if (!live) return;
     if (P.mode == 0) {
