@@ -65,33 +65,42 @@ template <int LOGN, int ROWS, bool SMEM_KEYS = false>
 __device__ __forceinline__ void mac_ginx(u32 (&acc)[(1 << LOGN) / 32], const u32 (&dg)[ROWS / 2][(1 << LOGN) / 32],
                                          const uint4* exch, const BrParams& P, const u32* ek1, const u32* ek2,
                                          const u32* mp, const u32* mn, int c, int lane) {
-    constexpr int N = 1 << LOGN, E = N / 32;
+    constexpr int N = 1 << LOGN, E = N / 32, ND = ROWS / 2;
     const u32 Q = P.C.Q, Q2 = P.C.Q2;
+    // this warp's digit polynomials are rows 2k+c, the partner's rows 2k+1-c: the (runtime) warp parity goes into the key
+    // row ADDRESS, not into a per-operand select of the digit
+    const uint4* k1o = reinterpret_cast<const uint4*>(ek1) + (size_t)(c * 2 + c) * (N / 4);         // row c,   component c
+    const uint4* k1p = reinterpret_cast<const uint4*>(ek1) + (size_t)((1 - c) * 2 + c) * (N / 4);   // row 1-c, component c
+    const uint4* k2o = reinterpret_cast<const uint4*>(ek2) + (size_t)(c * 2 + c) * (N / 4);
+    const uint4* k2p = reinterpret_cast<const uint4*>(ek2) + (size_t)((1 - c) * 2 + c) * (N / 4);
+    const uint4* xp  = exch + (1 - c) * (N / 4);
 #pragma unroll
     for (int v = 0; v < E / 4; ++v) {
-        uint4 k1[ROWS], k2[ROWS], dx[ROWS / 2];
+        uint4 o1[ND], p1[ND], o2[ND], p2[ND], dx[ND];
 #pragma unroll
-        for (int row = 0; row < ROWS; ++row) {
-            if (SMEM_KEYS) {   // ek1 / ek2 point into shared memory (GinxSmem::keys)
-                k1[row] = (reinterpret_cast<const uint4*>(ek1) + (row * 2 + c) * (N / 4))[v * 32 + lane];
-                k2[row] = (reinterpret_cast<const uint4*>(ek2) + (row * 2 + c) * (N / 4))[v * 32 + lane];
+        for (int k = 0; k < ND; ++k) {   // rows advance by 2 = 4 polynomials of N/4 vectors
+            if (SMEM_KEYS) {             // ek1 / ek2 point into shared memory (GinxSmem::keys)
+                o1[k] = k1o[k * N + v * 32 + lane]; p1[k] = k1p[k * N + v * 32 + lane];
+                o2[k] = k2o[k * N + v * 32 + lane]; p2[k] = k2p[k * N + v * 32 + lane];
             } else {
-                k1[row] = __ldg(reinterpret_cast<const uint4*>(ek1 + (size_t)(row * 2 + c) * N) + v * 32 + lane);
-                k2[row] = __ldg(reinterpret_cast<const uint4*>(ek2 + (size_t)(row * 2 + c) * N) + v * 32 + lane);
+                o1[k] = __ldg(k1o + k * N + v * 32 + lane); p1[k] = __ldg(k1p + k * N + v * 32 + lane);
+                o2[k] = __ldg(k2o + k * N + v * 32 + lane); p2[k] = __ldg(k2p + k * N + v * 32 + lane);
             }
         }
         const uint4 m1 = __ldg(reinterpret_cast<const uint4*>(mp) + v * 32 + lane);
         const uint4 m2 = __ldg(reinterpret_cast<const uint4*>(mn) + v * 32 + lane);
 #pragma unroll
-        for (int k = 0; k < ROWS / 2; ++k) dx[k] = exch[(2 * k + (1 - c)) * (N / 4) + v * 32 + lane];
+        for (int k = 0; k < ND; ++k) dx[k] = xp[2 * k * (N / 4) + v * 32 + lane];
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
             u64 s1 = 0, s2 = 0;
 #pragma unroll
-            for (int row = 0; row < ROWS; ++row) {
-                const u32 d = ((row & 1) == c) ? dg[row >> 1][4 * v + e] : comp4(dx[row >> 1], e);
-                s1          = mad_wide(d, comp4(k1[row], e), s1);
-                s2          = mad_wide(d, comp4(k2[row], e), s2);
+            for (int k = 0; k < ND; ++k) {
+                const u32 d = dg[k][4 * v + e], x = comp4(dx[k], e);
+                s1 = mad_wide(d, comp4(o1[k], e), s1);
+                s1 = mad_wide(x, comp4(p1[k], e), s1);
+                s2 = mad_wide(d, comp4(o2[k], e), s2);
+                s2 = mad_wide(x, comp4(p2[k], e), s2);
             }
             const u32 r1 = reduce64(s1, P.red_s, P.red_mu, Q);
             const u32 r2 = reduce64(s2, P.red_s, P.red_mu, Q);
@@ -106,23 +115,27 @@ __device__ __forceinline__ void mac_ginx(u32 (&acc)[(1 << LOGN) / 32], const u32
 template <int LOGN, int ROWS>
 __device__ __forceinline__ void mac_replace(u32 (&acc)[(1 << LOGN) / 32], const u32 (&dg)[ROWS / 2][(1 << LOGN) / 32],
                                             const uint4* exch, const BrParams& P, const u32* ek, int c, int lane) {
-    constexpr int N = 1 << LOGN, E = N / 32;
+    constexpr int N = 1 << LOGN, E = N / 32, ND = ROWS / 2;
     const u32 Q = P.C.Q, Q2 = P.C.Q2;
+    const uint4* ko = reinterpret_cast<const uint4*>(ek) + (size_t)(c * 2 + c) * (N / 4);         // own rows 2k+c
+    const uint4* kp = reinterpret_cast<const uint4*>(ek) + (size_t)((1 - c) * 2 + c) * (N / 4);   // partner rows 2k+1-c
+    const uint4* xp = exch + (1 - c) * (N / 4);
 #pragma unroll
     for (int v = 0; v < E / 4; ++v) {
-        uint4 k1[ROWS], dx[ROWS / 2];
+        uint4 o1[ND], p1[ND], dx[ND];
 #pragma unroll
-        for (int row = 0; row < ROWS; ++row)
-            k1[row] = __ldg(reinterpret_cast<const uint4*>(ek + (size_t)(row * 2 + c) * N) + v * 32 + lane);
-#pragma unroll
-        for (int k = 0; k < ROWS / 2; ++k) dx[k] = exch[(2 * k + (1 - c)) * (N / 4) + v * 32 + lane];
+        for (int k = 0; k < ND; ++k) {
+            o1[k] = __ldg(ko + k * N + v * 32 + lane);
+            p1[k] = __ldg(kp + k * N + v * 32 + lane);
+            dx[k] = xp[2 * k * (N / 4) + v * 32 + lane];
+        }
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
             u64 s1 = 0;
 #pragma unroll
-            for (int row = 0; row < ROWS; ++row) {
-                const u32 d = ((row & 1) == c) ? dg[row >> 1][4 * v + e] : comp4(dx[row >> 1], e);
-                s1          = mad_wide(d, comp4(k1[row], e), s1);
+            for (int k = 0; k < ND; ++k) {
+                s1 = mad_wide(dg[k][4 * v + e], comp4(o1[k], e), s1);
+                s1 = mad_wide(comp4(dx[k], e), comp4(p1[k], e), s1);
             }
             acc[4 * v + e] = csub(reduce64(s1, P.red_s, P.red_mu, Q), Q2);
         }
