@@ -95,7 +95,30 @@ __device__ __forceinline__ void permute_eval(u32 (&x)[(1 << LOGN) / 32], u32* sc
     __syncwarp();
 }
 
-// acc[c] (+)= sum_d dig[d] * ak[d][c]   (dig from registers for the producing warp, from exch for the other)
+// acc[c] (+)= sum_d dig[d] * ak[d][c]; digits LO <= d < HI are this warp's own (registers), the others come from exch
+template <int LOGN, int ND, int LO, int HI, bool ADD>
+__device__ __forceinline__ void mac_auto_split(u32 (&acc)[(1 << LOGN) / 32], const u32 (&dg)[ND][(1 << LOGN) / 32],
+                                               const uint4* exch, const BrParams& P, const u32* ak, int c, int lane) {
+    constexpr int N = 1 << LOGN, E = N / 32;
+    const u32 Q = P.C.Q, Q2 = P.C.Q2;
+#pragma unroll
+    for (int v = 0; v < E / 4; ++v) {
+        uint4 k1[ND], dx[ND];
+#pragma unroll
+        for (int d = 0; d < ND; ++d) {
+            k1[d] = __ldg(reinterpret_cast<const uint4*>(ak + (size_t)(d * 2 + c) * N) + v * 32 + lane);
+            if (d < LO || d >= HI) dx[d] = exch[d * (N / 4) + v * 32 + lane];
+        }
+#pragma unroll
+        for (int e = 0; e < 4; ++e) {
+            u64 s = ADD ? (u64)acc[4 * v + e] : 0ull;
+#pragma unroll
+            for (int d = 0; d < ND; ++d)
+                s = mad_wide((d >= LO && d < HI) ? dg[d][4 * v + e] : comp4(dx[d], e), comp4(k1[d], e), s);
+            acc[4 * v + e] = csub(reduce64(s, P.red_s, P.red_mu, Q), Q2);
+        }
+    }
+}
 template <int LOGN, int ND, bool FROM_REGS, bool ADD>
 __device__ __forceinline__ void mac_auto(u32 (&acc)[(1 << LOGN) / 32], const u32 (&dg)[ND][(1 << LOGN) / 32], const uint4* exch,
                                          const BrParams& P, const u32* ak, int c, int lane) {
@@ -129,7 +152,7 @@ __global__ void __launch_bounds__(64 * CTS, 1)
 br_sched_kernel(const __grid_constant__ BrParams P) {
     using W         = WNtt<LOGN, LOGH>;
     using S         = BrSmem<LOGN, LOGH, ROWS, CTS>;
-    constexpr int N = W::N, E = W::E, ND = ROWS / 2;
+    constexpr int N = W::N, E = W::E, ND = ROWS / 2, K0 = (ND + 1) / 2;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     S& sm = *reinterpret_cast<S*>(smem_raw);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -175,7 +198,11 @@ br_sched_kernel(const __grid_constant__ BrParams P) {
         } else if (ty == OP_PERM1) {
             if (c == 1) permute_eval<LOGN, LOGH>(acc, scratch, P.automap + (size_t)arg * N, lane);
         } else if (ty == OP_AUTO) {  // Automorphism(a = 5^arg or 2N-5), rgsw-acc-lmkcdey.cpp:257-287
+            // Only component 0 is key-switched, so its warp would run INTT + ND forward transforms while the partner
+            // idles.  The partner takes the upper digit polynomial instead: warp 0 hands it over in COEFFICIENT form
+            // through the exchange rows an automorphism round leaves unused (ND..), one warp-pair barrier in between.
             permute_eval<LOGN, LOGH>(acc, scratch, P.automap + (size_t)arg * N, lane);
+            uint4* raw = exch + ND * (N / 4);
             if (c == 0) {
                 W::inverse(acc, P.C, scratch, sm.twiB, P.twifull, lane);  // cta -> COEFFICIENT, canonical
 #pragma unroll
@@ -186,21 +213,39 @@ br_sched_kernel(const __grid_constant__ BrParams P) {
                     for (int k = 0; k < ND; ++k) dg[k][r] = d[k];
                 }
 #pragma unroll
-                for (int k = 0; k < ND; ++k) {
-                    W::template forward<1>(dg[k], P.C, scratch, sm.twB, P.twfull, lane);
-                    uint4* dst = exch + k * (N / 4);
+                for (int k = K0; k < ND; ++k)
 #pragma unroll
                     for (int v = 0; v < E / 4; ++v)
-                        dst[v * 32 + lane] = make_uint4(dg[k][4 * v], dg[k][4 * v + 1], dg[k][4 * v + 2], dg[k][4 * v + 3]);
-                }
-                mac_auto<LOGN, ND, true, false>(acc, dg, exch, P, P.bsk + P.auto_off + (size_t)arg * ablock, 0, lane);
+                        raw[(k - K0) * (N / 4) + v * 32 + lane] =
+                            make_uint4(dg[k][4 * v], dg[k][4 * v + 1], dg[k][4 * v + 2], dg[k][4 * v + 3]);
+            }
+            pair_barrier(1 + slot);
+            if (c == 1) {
+#pragma unroll
+                for (int k = K0; k < ND; ++k)
+#pragma unroll
+                    for (int v = 0; v < E / 4; ++v) {
+                        const uint4 t = raw[(k - K0) * (N / 4) + v * 32 + lane];
+                        dg[k][4 * v] = t.x; dg[k][4 * v + 1] = t.y; dg[k][4 * v + 2] = t.z; dg[k][4 * v + 3] = t.w;
+                    }
+            }
+#pragma unroll
+            for (int k = 0; k < ND; ++k) {
+                if ((k < K0) != (c == 0)) continue;   // warp 0: digits < K0, warp 1: the rest
+                W::template forward<1>(dg[k], P.C, scratch, sm.twB, P.twfull, lane);
+                uint4* dst = exch + k * (N / 4);
+#pragma unroll
+                for (int v = 0; v < E / 4; ++v)
+                    dst[v * 32 + lane] = make_uint4(dg[k][4 * v], dg[k][4 * v + 1], dg[k][4 * v + 2], dg[k][4 * v + 3]);
             }
         }
         __syncthreads();
         if (ty == OP_EXT) {
             mac_replace<LOGN, ROWS>(acc, dg, exch, P, P.bsk + (size_t)arg * kblock, c, lane);
-        } else if (ty == OP_AUTO && c == 1) {
-            mac_auto<LOGN, ND, false, true>(acc, dg, exch, P, P.bsk + P.auto_off + (size_t)arg * ablock, 1, lane);
+        } else if (ty == OP_AUTO) {
+            const u32* ak = P.bsk + P.auto_off + (size_t)arg * ablock;
+            if (c == 0) mac_auto_split<LOGN, ND, 0, K0, false>(acc, dg, exch, P, ak, 0, lane);
+            else        mac_auto_split<LOGN, ND, K0, ND, true>(acc, dg, exch, P, ak, 1, lane);
         }
         if (!done) ++pc;
     }
