@@ -338,9 +338,9 @@ def main():
         pass
     roofline = {"bound": "int32-pipe", "kernel": "br_ginx_kernel", "achieved": achieved / 1e12, "peak": imad.value / 1e12,
                 "unit": "TIMAD/s", "frac": achieved / imad.value if imad.value else None,
-                # DRAM bytes of one br_ginx launch at this batch size, from the ncu pass in profiles/r1_dram_v1.csv
+                # DRAM bytes of one br_ginx launch at this batch size, from the ncu pass in profiles/r1_launches_v3.csv
                 # (196 MB read + 252 MB written; algorithmic: 132 MB masks + 269 MB extracted cts + 41 MB keys/monomials)
-                "traffic": 447.9e6 if G == 65536 else None, "traffic_unit": "bytes/launch (profiles/r1_dram_v1.csv)",
+                "traffic": 438.7e6 if G == 65536 else None, "traffic_unit": "bytes/launch (profiles/r1_launches_v3.csv: 189.3 MB read + 249.4 MB written)",
                 "peak_source": "luxb200_intpipe_probe (dependent IMAD chains, measured live on this GPU)",
                 "algorithmic_imad_per_gate": IMAD_PER_GATE, "kernel_ms_per_step": br_ms / args.steps,
                 "kernel_share_of_step": br_ms * 1e-3 / t_dev,
