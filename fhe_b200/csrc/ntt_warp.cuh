@@ -187,6 +187,96 @@ struct WNtt {
         }
     }
 
+    // ---- forward of NP polynomials at once (same contract as forward<B0> for each) ---------------------------------
+    // The NP transforms advance butterfly by butterfly together: every twiddle is fetched once for all of them and each
+    // dependent chain has NP-1 independent ones to hide behind (3 warps per scheduler leave ~20 % of issue slots waiting
+    // on fixed latencies otherwise).  sm[p]: N u32 of scratch per polynomial, private to this warp.
+    template <int B0, int NP>
+    __device__ static __forceinline__ void forward_multi(u32 (&x)[NP][E], const NttConsts& C, u32* const (&sm)[NP],
+                                                         const uint2* twB, const uint2* __restrict__ twfull, int lane) {
+        const u32 Q = C.Q, Q2 = C.Q2;
+        int bound = B0;
+#pragma unroll
+        for (int s = LOGE - 1; s >= 0; --s) {
+            if (bound + 2 > H) {
+#pragma unroll
+                for (int p = 0; p < NP; ++p)
+#pragma unroll
+                    for (int r = 0; r < E; ++r) x[p][r] = ladder_2q(x[p][r], bound, C);
+                bound = 2;
+            }
+#pragma unroll
+            for (int qq = 0; qq < E / 2; ++qq) {
+                const int tr = 1 << s, i = qq >> s, r = (i << (s + 1)) | (qq & (tr - 1));
+                const uint2 w = C.twA[(E >> (s + 1)) + i];
+#pragma unroll
+                for (int p = 0; p < NP; ++p) ct(x[p][r], x[p][r + tr], w.x, w.y, Q, Q2);
+            }
+            bound += 2;
+        }
+        if (E < 32) {
+#pragma unroll
+            for (int t = 16; t >= E; t >>= 1) {
+                if (bound + 2 > H) {
+#pragma unroll
+                    for (int p = 0; p < NP; ++p)
+#pragma unroll
+                        for (int r = 0; r < E; ++r) x[p][r] = ladder_2q(x[p][r], bound, C);
+                    bound = 2;
+                }
+                const bool hi = lane & t;
+#pragma unroll
+                for (int r = 0; r < E; ++r) {
+                    const uint2 w = twfull[N / (2 * t) + (32 * r + lane) / (2 * t)];
+#pragma unroll
+                    for (int p = 0; p < NP; ++p) {
+                        u32 u   = shoup_mul(x[p][r], w.x, w.y, Q);
+                        u32 v   = __shfl_xor_sync(0xffffffffu, hi ? u : x[p][r], t);
+                        x[p][r] = hi ? (v - u + Q2) : (x[p][r] + v);
+                    }
+                }
+                bound += 2;
+            }
+        }
+        __syncwarp();
+#pragma unroll
+        for (int p = 0; p < NP; ++p) store_A(sm[p], x[p], lane);
+        __syncwarp();
+#pragma unroll
+        for (int p = 0; p < NP; ++p) load_B(sm[p], x[p], lane);
+#pragma unroll
+        for (int s = LOGTB; s >= 0; --s) {
+            if (bound + 2 > H) {
+#pragma unroll
+                for (int p = 0; p < NP; ++p)
+#pragma unroll
+                    for (int r = 0; r < E; ++r) x[p][r] = ladder_2q(x[p][r], bound, C);
+                bound = 2;
+            }
+            if (s == 0 && bound > 2) {
+#pragma unroll
+                for (int p = 0; p < NP; ++p)
+#pragma unroll
+                    for (int qq = 0; qq < E / 2; ++qq) x[p][2 * qq] = ladder_2q(x[p][2 * qq], bound, C);
+                bound = 2;
+            }
+#pragma unroll
+            for (int qq = 0; qq < E / 2; ++qq) {
+                const int t = 1 << s, i = qq >> s, r = (i << (s + 1)) | (qq & (t - 1));
+                const uint2 w = twB[(offB(t) + i) * 32 + lane];
+#pragma unroll
+                for (int p = 0; p < NP; ++p) ct(x[p][r], x[p][r + t], w.x, w.y, Q, Q2);
+            }
+            bound += 2;
+        }
+        if (bound > 2) {
+#pragma unroll
+            for (int p = 0; p < NP; ++p)
+#pragma unroll
+                for (int r = 0; r < E; ++r) x[p][r] = ladder_2q(x[p][r], bound, C);
+        }
+    }
+
     // ---- inverse: layout B in (values in [0, 2Q)), layout A out, canonical [0, Q) --------------------------
     // Gentleman-Sande: a' = a + b doubles the bound of the sum path, b' = (a - b + kQ) * w comes back < 2Q.  Bounds are
     // tracked PER REGISTER at compile time: after j stages only the registers whose low j index bits are 0 carry the
