@@ -201,6 +201,15 @@ void luxb200_ctx_destroy(luxb200_ctx* c) {
                       &c->tmpc, &c->tmpd};
     for (DevBuf* b : bufs) b->release();
     c->ntt.release();
+    for (int s = 0; s < 2; ++s) {
+        for (DevBuf& b : c->pipe.in[s]) b.release();
+        for (DevBuf& b : c->pipe.st[s]) b.release();
+        for (cudaEvent_t e : {c->pipe.e_in[s], c->pipe.e_free[s], c->pipe.e_stage[s], c->pipe.e_out[s]})
+            if (e) cudaEventDestroy(e);
+    }
+    for (cudaEvent_t e : c->pipe.tev) cudaEventDestroy(e);
+    if (c->pipe.s_in) cudaStreamDestroy(c->pipe.s_in);
+    if (c->pipe.s_out) cudaStreamDestroy(c->pipe.s_out);
     for (int i = 0; i < 5; ++i)
         if (c->ev[i]) cudaEventDestroy(c->ev[i]);
     if (c->stream) cudaStreamDestroy(c->stream);

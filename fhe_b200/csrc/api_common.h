@@ -79,6 +79,15 @@ struct luxb200_ctx {
     uint64_t launches = 0;
     float t_prep = 0, t_br = 0, t_ks = 0, t_total = 0;
     uint32_t last_launches = 0;
+    // host-buffer pipeline (luxb200_evalbingate_batch with large batches): copy-in / copy-out streams, two input landing
+    // sets and two output staging sets, so the PCIe copies of chunk k+1 / k-1 run under the kernels of chunk k
+    struct HostPipe {
+        cudaStream_t s_in = nullptr, s_out = nullptr;
+        cudaEvent_t e_in[2] = {}, e_free[2] = {}, e_stage[2] = {}, e_out[2] = {};
+        DevBuf in[2][4], st[2][2];
+        std::vector<cudaEvent_t> tev;   // 4 timing events per chunk
+        bool ready = false;
+    } pipe;
 };
 
 int lb_set_device(int device);

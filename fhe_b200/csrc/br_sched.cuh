@@ -119,29 +119,6 @@ __device__ __forceinline__ void mac_auto_split(u32 (&acc)[(1 << LOGN) / 32], con
         }
     }
 }
-template <int LOGN, int ND, bool FROM_REGS, bool ADD>
-__device__ __forceinline__ void mac_auto(u32 (&acc)[(1 << LOGN) / 32], const u32 (&dg)[ND][(1 << LOGN) / 32], const uint4* exch,
-                                         const BrParams& P, const u32* ak, int c, int lane) {
-    constexpr int N = 1 << LOGN, E = N / 32;
-    const u32 Q = P.C.Q, Q2 = P.C.Q2;
-#pragma unroll
-    for (int v = 0; v < E / 4; ++v) {
-        uint4 k1[ND], dx[ND];
-#pragma unroll
-        for (int d = 0; d < ND; ++d) {
-            k1[d] = __ldg(reinterpret_cast<const uint4*>(ak + (size_t)(d * 2 + c) * N) + v * 32 + lane);
-            if (!FROM_REGS) dx[d] = exch[d * (N / 4) + v * 32 + lane];
-        }
-#pragma unroll
-        for (int e = 0; e < 4; ++e) {
-            u64 s = ADD ? (u64)acc[4 * v + e] : 0ull;
-#pragma unroll
-            for (int d = 0; d < ND; ++d) s = mad_wide(FROM_REGS ? dg[d][4 * v + e] : comp4(dx[d], e), comp4(k1[d], e), s);
-            acc[4 * v + e] = csub(reduce64(s, P.red_s, P.red_mu, Q), Q2);
-        }
-    }
-}
-
 // ---- scheduled kernel ------------------------------------------------------------------------------------------
 // One 2*CTS-warp CTA per SM, like br_ginx_kernel.  Ciphertexts walk their own op lists, but the CTA advances in
 // rounds with exactly two CTA-wide barriers per round whatever the op type, so the warps of an SM sub-partition stay

@@ -228,6 +228,32 @@ def test_std128_full_batch_properties():
     ctx.close(); oc.close()
 
 
+@pytest.mark.parametrize("extended", [False, True])
+def test_host_pipeline_ragged(extended):
+    """host-buffer batches >= 2*16384 gates go through the 3-stream chunk pipeline (double-buffered landing/staging
+    sets, chunks of whole blind-rotation waves): a ragged 3.x-chunk batch must equal the same gates evaluated in small
+    non-pipelined calls, bit for bit."""
+    from fhe_b200.context import BinFHEContext
+    from fhe_b200 import keygen as kg
+    ctx = BinFHEContext().GenerateBinFHEContext("TOY", "GINX")
+    ks = kg.keygen(ctx, seed=5)
+    ctx.BTKeyLoad(ks.bsk, ks.kskA, ks.kskB)
+    G = 3 * 16384 + 77
+    rng = np.random.default_rng(11)
+    m1 = rng.integers(0, 2, G); m2 = rng.integers(0, 2, G)
+    a1, b1 = kg.encrypt(ctx, ks.sk, m1, rng); a2, b2 = kg.encrypt(ctx, ks.sk, m2, rng)
+    (oa, ob), res = ctx.EvalBinGateBatch("XOR", (a1, b1), (a2, b2), extended=extended)
+    assert res.success, res.error
+    for lo in range(0, G, 8192):    # pieces below the pipeline threshold take the single-stream path
+        hi = min(G, lo + 8192)
+        (xa, xb), r2 = ctx.EvalBinGateBatch("XOR", (a1[lo:hi].copy(), b1[lo:hi].copy()), (a2[lo:hi].copy(), b2[lo:hi].copy()),
+                                            extended=extended)
+        assert r2.success and (oa[lo:hi] == xa).all() and (ob[lo:hi] == xb).all(), lo
+    if not extended:
+        assert (kg.decrypt(ctx, ks.sk, oa, ob) == (m1 ^ m2)).all()
+    ctx.close()
+
+
 def test_ntt_full_size_linearity():
     """65536 polynomials at N=1024 (BASELINE configs[1]): NTT(a) + NTT(b) == NTT(a + b) and inverse(forward) == id"""
     from fhe_b200.context import NTTPlan
