@@ -180,6 +180,37 @@ def compare8(name, method, pairs):
             "decrypt_errors": int((dec != exp).sum())}
 
 
+def compare8_circuit(name, method, pairs):
+    """The same GreaterThan8 circuit through luxb200_circuit_batch (BatchDAG on the device): one call with HOST buffers;
+    the 17 input wires go up, 25 levels run back to back on the context stream with every intermediate in HBM, one wire
+    comes back.  Timed end to end (H2D + D2H inside)."""
+    from fhe_b200.circuits import greater_than8, plain_circuit
+    ctx = BinFHEContext().GenerateBinFHEContext(name, method)
+    ks = kg.keygen(ctx, seed=31)
+    ctx.BTKeyLoad(ks.bsk, ks.kskA, ks.kskB)
+    rng = np.random.default_rng(8)
+    va = rng.integers(0, 256, pairs); vb = np.where(rng.integers(0, 2, pairs) == 1, rng.integers(0, 256, pairs), va ^ (1 << rng.integers(0, 8, pairs)))
+    bits = np.concatenate([((va[None, :] >> np.arange(8)[:, None]) & 1), ((vb[None, :] >> np.arange(8)[:, None]) & 1),
+                           np.zeros((1, pairs), np.int64)])
+    in_a = torch.empty((17, pairs, ctx.n), dtype=torch.int64).pin_memory().numpy().view(np.uint64)
+    in_b = torch.empty((17, pairs), dtype=torch.int64).pin_memory().numpy().view(np.uint64)
+    for i in range(17):
+        in_a[i], in_b[i] = kg.encrypt(ctx, ks.sk, bits[i], rng)
+    gates, out = greater_than8()
+    ctx.EvalCircuitBatch(17, gates, [out], in_a[:, :64], in_b[:, :64])   # warm-up
+    t0 = time.perf_counter()
+    (oa, ob), res = ctx.EvalCircuitBatch(17, gates, [out], in_a, in_b)
+    dt = time.perf_counter() - t0
+    assert res.success, res.error
+    st = ctx.CircuitStats()
+    dec = kg.decrypt(ctx, ks.sk, oa[0], ob[0])
+    exp = plain_circuit(gates, bits)[out]
+    ctx.close()
+    return {"workload": f"{name}/{method} GreaterThan8 x{pairs} as ONE luxb200_circuit_batch call (host buffers)",
+            "comparisons_per_s": pairs / dt, "bootstraps_per_s": 48 * pairs / dt, "seconds": dt, "levels": st["levels"],
+            "launches": st["launches"], "decrypt_errors": int((dec != exp).sum())}
+
+
 if __name__ == "__main__":
     which = sys.argv[1:] or ["ntt32", "ntt64", "methods", "compare"]
     if "ntt32" in which:
@@ -192,6 +223,9 @@ if __name__ == "__main__":
     if "compare" in which:
         print(json.dumps(compare8("STD128", "GINX", 4096)))
         print(json.dumps(compare8("STD128_LMKCDEY", "LMKCDEY", 4096)))
+    if "circuit" in which:
+        print(json.dumps(compare8_circuit("STD128", "GINX", 4096)))
+        print(json.dumps(compare8_circuit("STD128_LMKCDEY", "LMKCDEY", 4096)))
     if "methods" in which:
         print(json.dumps(method_gates("STD128_LMKCDEY", "LMKCDEY", 16384)))
         print(json.dumps(method_gates("STD128_AP", "AP", 4096)))

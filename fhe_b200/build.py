@@ -9,36 +9,72 @@ CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libluxb200.so")
 NVCC = os.environ.get("NVCC", "/usr/local/cuda/bin/nvcc")
 FLAGS = ["-std=c++17", "-O3", "-lineinfo", "-gencode", "arch=compute_100a,code=sm_100a", "-Xcompiler", "-fPIC",
-         "-shared", "--expt-relaxed-constexpr", "-Xptxas", "-v"]
+         "--expt-relaxed-constexpr", "-Xptxas", "-v"]
+OBJ = os.path.join(HERE, "_obj")
+# translation units: api.cu holds every kernel of the bootstrapping / NTT path (minutes to compile); circuit.cu is the
+# level scheduler above it
+UNITS = ["api.cu", "circuit.cu"]
 
 
 def sources():
-    return [os.path.join(CSRC, "api.cu")]
+    return [os.path.join(CSRC, u) for u in UNITS]
+
+
+def _newest_dep(unit):
+    """api.cu includes every other file of csrc/; circuit.cu only the headers."""
+    t = os.path.getmtime(os.path.join(HERE, "..", "include", "luxb200.h"))
+    for f in os.listdir(CSRC):
+        if f.endswith(".cu") and f != unit:
+            continue
+        if unit != "api.cu" and f.endswith(".inc"):
+            continue
+        t = max(t, os.path.getmtime(os.path.join(CSRC, f)))
+    return t
+
+
+def _obj(unit):
+    return os.path.join(OBJ, unit.replace(".cu", ".o"))
+
+
+def _stale(unit):
+    o = _obj(unit)
+    return not os.path.exists(o) or os.path.getmtime(o) < _newest_dep(unit)
 
 
 def needs_build():
     if not os.path.exists(OUT):
         return True
-    t = os.path.getmtime(OUT)
-    for f in os.listdir(CSRC):
-        if os.path.getmtime(os.path.join(CSRC, f)) > t:
-            return True
-    return os.path.getmtime(os.path.join(HERE, "..", "include", "luxb200.h")) > t
+    return any(_stale(u) for u in UNITS) or any(os.path.getmtime(_obj(u)) > os.path.getmtime(OUT) for u in UNITS)
 
 
 def build(force=False, verbose=False):
     if not force and not needs_build():
         return OUT
-    cmd = [NVCC] + FLAGS + ["-o", OUT] + sources()
-    r = subprocess.run(cmd, capture_output=True, text=True)
+    os.makedirs(OBJ, exist_ok=True)
     log = os.path.join(HERE, "build.log")
+    text = ""
+    procs = []
+    for u in UNITS:
+        if force or _stale(u):
+            cmd = [NVCC] + FLAGS + ["-c", "-o", _obj(u), os.path.join(CSRC, u)]
+            procs.append((cmd, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
+    failed = False
+    for cmd, p in procs:
+        out = p.communicate()[0]
+        text += " ".join(cmd) + "\n" + out
+        failed |= p.returncode != 0
+    if not failed:
+        cmd = [NVCC, "-shared", "-o", OUT] + [_obj(u) for u in UNITS]
+        r = subprocess.run(cmd, capture_output=True, text=True)
+        text += " ".join(cmd) + "\n" + r.stdout + r.stderr
+        failed = r.returncode != 0
     with open(log, "w") as f:
-        f.write(" ".join(cmd) + "\n" + r.stdout + r.stderr)
-    if r.returncode != 0:
-        sys.stderr.write(r.stdout + r.stderr)
+        f.write(text)
+    if failed:
+        sys.stderr.write(text)
         raise RuntimeError("nvcc failed; see " + log)
     if verbose:
-        print(r.stderr)
+        print(text)
     return OUT
 
 

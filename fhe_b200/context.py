@@ -183,6 +183,31 @@ class BinFHEContext:
         return out
 
     # -- device-resident operators (uint32 tensors already in HBM; pointers as ints) ------------------------
+    # -- gate circuits (BatchDAG, binfhe-batch.h:255-279) ------------------------------------------------
+    def EvalCircuitBatch(self, n_inputs, gates, outputs, in_a, in_b):
+        """One circuit over `count` independent input sets, level-scheduled on the device with device-resident
+        intermediates (luxb200_circuit_batch).  gates: [(op, in0, in1)], op a 2-input gate name, "NOT" or "BOOTSTRAP";
+        wire ids as BatchDAG hands them out (inputs 0..n_inputs-1, then one per gate).  in_a [n_inputs][count][n],
+        in_b [n_inputs][count]; returns ((out_a [n_outputs][count][n], out_b [n_outputs][count]), BatchResult)."""
+        ops = {"NOT": 100, "BOOTSTRAP": 101}
+        g = np.zeros((max(len(gates), 1), 3), np.uint32)
+        for k, (op, i0, i1) in enumerate(gates):
+            g[k] = (ops[op] if op in ops else _l.GATE[op], i0, i1 if i1 is not None else 0)
+        outs = np.ascontiguousarray(outputs, dtype=np.uint32)
+        in_a, in_b = self._u64(in_a), self._u64(in_b)
+        assert in_b.shape[0] == n_inputs and in_a.shape[:2] == in_b.shape
+        cnt = in_b.shape[1]
+        oa = np.empty((len(outs), cnt, self.n), np.uint64)
+        ob = np.empty((len(outs), cnt), np.uint64)
+        rc = self.L.luxb200_circuit_batch(self.h, n_inputs, _l.ptr(g), len(gates), _l.ptr(outs), len(outs), _l.ptr(in_a),
+                                          _l.ptr(in_b), _l.ptr(oa), _l.ptr(ob), cnt)
+        return (oa, ob), self._result(rc, len(gates) * cnt)
+
+    def CircuitStats(self):
+        t = np.zeros(3, np.uint64)
+        _l.check(self.L.luxb200_circuit_last_stats(self.h, _l.ptr(t)))
+        return {"levels": int(t[0]), "bootstrapped_gates": int(t[1]), "launches": int(t[2])}
+
     def EvalBinGateBatchDev(self, gate, a1, b1, a2, b2, oa, ob, count):
         _l.check(self.L.luxb200_evalbingate_batch_dev(self.h, _l.GATE[gate], _l.VP(a1), _l.VP(b1), _l.VP(a2), _l.VP(b2),
                                                       _l.VP(oa), _l.VP(ob), count))

@@ -198,7 +198,7 @@ void luxb200_ctx_destroy(luxb200_ctx* c) {
     cudaSetDevice(c->device);
     DevBuf* bufs[] = {&c->bsk, &c->mono, &c->kskA, &c->kskB, &c->automap, &c->loggen, &c->in0, &c->in1, &c->in2, &c->in3, &c->wa,
                       &c->wb, &c->lut, &c->ext, &c->oa, &c->ob, &c->o64a, &c->o64b, &c->sched, &c->tmpa, &c->tmpb,
-                      &c->tmpc, &c->tmpd};
+                      &c->tmpc, &c->tmpd, &c->cpa, &c->cpb, &c->cdesc, &c->clsel};
     for (DevBuf* b : bufs) b->release();
     c->ntt.release();
     for (int s = 0; s < 2; ++s) {

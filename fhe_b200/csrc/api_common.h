@@ -76,9 +76,11 @@ struct luxb200_ctx {
     bool have_bsk = false, have_ksk = false;
     // work buffers
     DevBuf in0, in1, in2, in3, wa, wb, lut, ext, oa, ob, o64a, o64b, sched, tmpa, tmpb, tmpc, tmpd;
+    DevBuf cpa, cpb, cdesc, clsel;   // gate circuits (circuit.cu): wire pool (a, b), gate descriptors, per-item table offsets
     uint64_t launches = 0;
     float t_prep = 0, t_br = 0, t_ks = 0, t_total = 0;
     uint32_t last_launches = 0;
+    uint64_t circ_stats[3] = {0, 0, 0};   // levels, bootstrapped gates, launches of the last circuit call
     // host-buffer pipeline (luxb200_evalbingate_batch with large batches): copy-in / copy-out streams, two input landing
     // sets and two output staging sets, so the PCIe copies of chunk k+1 / k-1 run under the kernels of chunk k
     struct HostPipe {
@@ -91,3 +93,14 @@ struct luxb200_ctx {
 };
 
 int lb_set_device(int device);
+
+// ---- entry points of api.cu used by circuit.cu (a separate translation unit, same library) -------------------
+// test-vector table of a 2-input gate for plaintext modulus p (binfhe-base-scheme.cpp:535-567)
+void lb_gate_lut(const luxb200_ctx* c, int gate, uint64_t p, std::vector<uint32_t>& lut);
+int lb_upload_lut(luxb200_ctx* c, const std::vector<uint32_t>& lut);
+// blind rotation + extraction + SwitchCTtoqn on prepared device inputs; lutsel: optional per-item offsets into c->lut
+int lb_boot_dev(luxb200_ctx* c, const uint32_t* d_a, const uint32_t* d_b, uint64_t ctmod, uint64_t b_add, uint64_t fmod,
+                uint32_t* d_oa, uint32_t* d_ob, uint64_t count, const uint32_t* lutsel);
+int lb_download_rows(luxb200_ctx* c, const uint32_t* d_in, uint32_t in_stride, uint32_t in_off, uint32_t len, uint64_t count,
+                     DevBuf& stage, uint64_t* host);
+uint64_t lb_wave(luxb200_ctx* c);   // ciphertexts one blind-rotation wave holds (SMs x ciphertexts per CTA)

@@ -20,6 +20,7 @@ struct BrParams {
     const u32* a;          // [count][n]  LWE mask mod ctmod
     const u32* b;          // [count]
     const u32* lut;        // [ctmod] test-vector table: m[j*factor] = lut[(b - j) mod ctmod]
+    const u32* lutsel;     // optional [count]: element offset of ciphertext ct's table inside lut (gate circuits mix gate kinds)
     const u32* sched;      // AP/LMKCDEY: per-ciphertext op list [count][sched_stride]
     const u32* automap;    // LMKCDEY: [numAutoKeys+1][sigma(N)] source indices of the EVALUATION-format automorphisms
     u32* ext;              // [count][N+1] : a' (N coefficients mod Q) then b

@@ -164,6 +164,7 @@ __device__ __forceinline__ void prologue(u32 (&acc)[(1 << LOGN) / 32], const BrP
         return;
     }
     const u32 b = P.b[ct], half = P.ctmod >> 1;
+    const u32* lut = P.lutsel ? P.lut + P.lutsel[ct] : P.lut;
     u32 m[E];
 #pragma unroll
     for (int r = 0; r < E; ++r) {
@@ -171,7 +172,7 @@ __device__ __forceinline__ void prologue(u32 (&acc)[(1 << LOGN) / 32], const BrP
         u32 val     = 0;
         if (j % P.factor == 0) {
             const u32 jj = j / P.factor;
-            if (jj < half) val = P.lut[(b + P.ctmod - jj) % P.ctmod];
+            if (jj < half) val = lut[(b + P.ctmod - jj) % P.ctmod];
         }
         m[r] = val;
     }

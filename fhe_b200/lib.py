@@ -63,6 +63,8 @@ SIGNATURES = {
     "luxb200_ntt_plan_sync": (INT, [VP]),
     "luxb200_ntt_last_ms": (C.c_float, [VP]),
     "luxb200_evalbingate_batch_dev": (INT, [VP, INT, VP, VP, VP, VP, VP, VP, U64]),
+    "luxb200_circuit_batch": (INT, [VP, U32, VP, U32, VP, U32, VP, VP, VP, VP, U64]),
+    "luxb200_circuit_last_stats": (INT, [VP, VP]),
     "luxb200_last_timing": (INT, [VP, VP]),
     "luxb200_launch_count": (U64, [VP]),
     "luxb200_intpipe_probe": (INT, [INT, C.POINTER(C.c_double), C.POINTER(C.c_double)]),

@@ -443,6 +443,16 @@ void BackendB200::Bootstrap(const std::vector<LWECiphertext>& in, std::vector<LW
           "Bootstrap");
     build_cts(oa, ob, p_.n, NativeInteger(p_.q), in[0]->GetptModulus(), out);
 }
+void BackendB200::EvalCircuit(const std::vector<LWECiphertext>& inputs, const std::vector<luxb200_gate>& gates,
+                              const std::vector<uint32_t>& outputs, std::vector<LWECiphertext>& out) {
+    if (outputs.empty()) { out.clear(); return; }
+    std::vector<uint64_t> a, b, oa(outputs.size() * size_t(p_.n)), ob(outputs.size());
+    flatten_cts(inputs, p_.n, a, b);   // [n_inputs][count = 1][n]
+    check(luxb200_circuit_batch(h_, static_cast<uint32_t>(inputs.size()), gates.data(), static_cast<uint32_t>(gates.size()),
+                                outputs.data(), static_cast<uint32_t>(outputs.size()), a.data(), b.data(), oa.data(), ob.data(),
+                                1), "EvalCircuit");
+    build_cts(oa, ob, p_.n, NativeInteger(p_.q), NativeInteger(4), out);
+}
 void BackendB200::EvalFunc(const std::vector<LWECiphertext>& in, const std::vector<NativeInteger>& lut, const NativeInteger& beta,
                            std::vector<LWECiphertext>& out) {
     if (in.empty()) { out.clear(); return; }

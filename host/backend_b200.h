@@ -77,6 +77,10 @@ public:
     void Bootstrap(const std::vector<LWECiphertext>& in, std::vector<LWECiphertext>& out);
     void EvalFunc(const std::vector<LWECiphertext>& in, const std::vector<NativeInteger>& lut, const NativeInteger& beta,
                   std::vector<LWECiphertext>& out);
+    // A gate DAG in one call (luxb200_circuit_batch, count = 1): wires 0 .. inputs.size()-1 are `inputs`, wire
+    // inputs.size() + g the result of gates[g]; out[k] = wire outputs[k].  Intermediates stay on the device.
+    void EvalCircuit(const std::vector<LWECiphertext>& inputs, const std::vector<luxb200_gate>& gates,
+                     const std::vector<uint32_t>& outputs, std::vector<LWECiphertext>& out);
 
 private:
     void check(int rc, const char* what) const;

@@ -5,8 +5,10 @@
 // are bit-identical.  BATCH_CPU_FORCE keeps the reference's own per-ciphertext loop (an explicit caller request,
 // not a fallback): without that flag a missing or unbound B200 backend is an error, never a silent CPU path.
 //
-// BatchDAG::Execute (sequential in the reference, batch.cpp:429-482) is a level scheduler here: operations are
-// levelled by data dependency and every level is issued as one batched call per (operation, gate | LUT).
+// BatchDAG::Execute (sequential in the reference, batch.cpp:429-482) is a level scheduler here.  A DAG made of 2-input
+// gates, Bootstrap and CMUX over plaintext-modulus-4 ciphertexts mod q goes to the device as ONE luxb200_circuit_batch
+// call (levels scheduled there, intermediates resident in HBM); anything else (EvalFunc nodes, other moduli) is levelled
+// on the host and every level issued as one batched call per (operation, gate | LUT).
 #include <algorithm>
 #include <future>
 #include <map>
@@ -195,11 +197,70 @@ size_t BatchDAG::AddCMUX(size_t sel_id, size_t true_id, size_t false_id) {
     return impl_->add(BatchOp::OP_CMUX, {sel_id, true_id, false_id});
 }
 
+namespace {
+bool gate2(BINGATE g) { return g == OR || g == AND || g == NOR || g == NAND || g == XOR || g == XNOR || g == XOR_FAST || g == XNOR_FAST; }
+}  // namespace
+
+// The whole DAG as one device-side circuit.  Returns false (nothing done) when the DAG holds something the circuit entry
+// point does not cover; throws what the per-operation path would throw.
+static bool execute_on_device(BinFHEContext& cc, std::vector<LWECiphertext>& cts, const std::vector<BatchOp>& ops,
+                              BatchResult& result) {
+    if (ops.empty()) return false;
+    const NativeInteger q = cc.GetParams()->GetLWEParams()->Getq();
+    std::vector<char> produced(cts.size(), 0);
+    for (const auto& op : ops) {
+        if (op.type == BatchOp::OP_BINGATE ? !gate2(op.gate) : (op.type != BatchOp::OP_BOOTSTRAP && op.type != BatchOp::OP_CMUX))
+            return false;
+        produced[op.output_ids[0]] = 1;
+    }
+    // wires: the DAG's input ciphertexts first, then one wire per gate (CMUX = NOT + 3 NAND, binfhe-base-scheme.cpp:176-183)
+    std::vector<uint32_t> wire(cts.size(), 0);
+    std::vector<LWECiphertext> inputs;
+    for (size_t id = 0; id < cts.size(); ++id) {
+        if (produced[id]) continue;
+        if (!cts[id]) return false;   // never referenced or a caller error: the per-operation path reports it
+        if (cts[id]->GetModulus() != q || cts[id]->GetptModulus() != NativeInteger(4)) return false;
+        wire[id] = static_cast<uint32_t>(inputs.size());
+        inputs.push_back(cts[id]);
+    }
+    if (inputs.empty()) return false;
+    std::vector<luxb200_gate> gates;
+    std::vector<uint32_t> outs;
+    const uint32_t ni = static_cast<uint32_t>(inputs.size());
+    auto emit = [&](uint32_t op, uint32_t a, uint32_t b) {
+        gates.push_back(luxb200_gate{op, a, b});
+        return ni + static_cast<uint32_t>(gates.size()) - 1;
+    };
+    for (const auto& op : ops) {
+        for (size_t id : op.input_ids)
+            if (id >= op.output_ids[0]) throw std::out_of_range("Invalid ciphertext ID");
+        uint32_t w;
+        if (op.type == BatchOp::OP_BINGATE) {
+            w = emit(static_cast<uint32_t>(op.gate), wire[op.input_ids[0]], wire[op.input_ids[1]]);
+        } else if (op.type == BatchOp::OP_BOOTSTRAP) {
+            w = emit(LUXB200_OP_BOOTSTRAP, wire[op.input_ids[0]], 0);
+        } else {   // EvalBinGate(CMUX, {v0, v1, v2}) = NAND(NAND(v0, NOT v2), NAND(v1, v2))
+            const uint32_t v0 = wire[op.input_ids[0]], v1 = wire[op.input_ids[1]], v2 = wire[op.input_ids[2]];
+            const uint32_t t  = emit(LUXB200_OP_NOT, v2, 0);
+            const uint32_t n1 = emit(NAND, v0, t), n2 = emit(NAND, v1, v2);
+            w = emit(NAND, n1, n2);
+        }
+        wire[op.output_ids[0]] = w;
+        outs.push_back(w);
+    }
+    std::vector<LWECiphertext> res;
+    b200()->EvalCircuit(inputs, gates, outs, res);
+    for (size_t i = 0; i < ops.size(); ++i) cts[ops[i].output_ids[0]] = res[i];
+    result.processed = ops.size();
+    return true;
+}
+
 BatchResult BatchDAG::Execute(uint32_t flags) {
     BatchResult result{true, 0, 0, ""};
     auto& cts = impl_->ciphertexts;
     auto& ops = impl_->operations;
     try {
+        if (!(flags & BATCH_CPU_FORCE) && execute_on_device(impl_->cc, cts, ops, result)) return result;
         // level of a ciphertext = 0 for inputs, 1 + max(level of operands) for an operation's output
         std::vector<size_t> level(cts.size(), 0);
         size_t depth = 0;

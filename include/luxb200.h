@@ -20,6 +20,8 @@
  *   luxb200_ntt_batch               PolyImpl::SwitchFormat                 src/core/include/lattice/hal/default/poly-impl.h:420-440
  *                                   (NumberTheoreticTransformNat, src/core/include/math/hal/intnat/transformnat-impl.h:302-373,511-624)
  *   luxb200_dcrt_ntt_batch          DCRTPolyImpl::SwitchFormat             src/core/include/lattice/hal/default/dcrtpoly-impl.h:1953-1959
+ *   luxb200_circuit_batch           lux::fhe::BatchDAG::Execute            binfhe-batch.h:255-279 (src/binfhe/lib/batch/batch.cpp:429-482,
+ *                                                                          sequential there): gate DAG, level-scheduled on the device
  *   luxb200_load_bsk / _ksk         backend::Backend::PackBootstrappingKey backend.h:223-233 (flat layouts below)
  *   luxb200_ctx_create              BinFHEContext::GenerateBinFHEContext   src/binfhe/lib/binfhecontext.cpp:109-187 (parameters only)
  *
@@ -147,6 +149,27 @@ int luxb200_evalbingate_batch_dev(luxb200_ctx* ctx, int gate, const uint32_t* a1
 int luxb200_last_timing(luxb200_ctx* ctx, float* out);
 /* cumulative number of kernels this library launched on the context (for bench.py's gpu_launches) */
 uint64_t luxb200_launch_count(luxb200_ctx* ctx);
+
+/* ---- gate circuits: lux::fhe::BatchDAG (binfhe-batch.h:255-279; Execute, batch.cpp:429-482) --------------------- */
+/* One circuit applied to `count` independent input sets.  Wires 0 .. n_inputs-1 are the inputs, wire n_inputs + g is the
+ * output of gates[g]; a gate may only read wires with a smaller id (the order BatchDAG::Add* produces).
+ * op: a 2-input BINGATE code (LUXB200_OR .. LUXB200_XNOR, *_FAST) = BinFHEScheme::EvalBinGate on (in0, in1);
+ *     LUXB200_OP_NOT = EvalNOT(in0) (binfhe-base-scheme.cpp:223-237, no bootstrap);
+ *     LUXB200_OP_BOOTSTRAP = BinFHEScheme::Bootstrap(in0) with plaintext modulus 4 (binfhe-base-scheme.cpp:190-220).
+ * Gates are grouped into dependency levels; one level = one gather kernel + one blind-rotation launch + one key-switch
+ * launch over every (gate, input set) pair of the level, mixed gate kinds included.  Every intermediate ciphertext stays in
+ * HBM; only the inputs go up and the wires listed in `outputs` come back.
+ * in_a [n_inputs][count][n], in_b [n_inputs][count] mod q; out_a [n_outputs][count][n], out_b [n_outputs][count]. */
+enum { LUXB200_OP_NOT = 100, LUXB200_OP_BOOTSTRAP = 101 };
+typedef struct {
+    uint32_t op;         /* BINGATE code or LUXB200_OP_* */
+    uint32_t in0, in1;   /* wire ids; in1 ignored by the 1-input ops */
+} luxb200_gate;
+int luxb200_circuit_batch(luxb200_ctx* ctx, uint32_t n_inputs, const luxb200_gate* gates, uint32_t n_gates,
+                          const uint32_t* outputs, uint32_t n_outputs, const uint64_t* in_a, const uint64_t* in_b,
+                          uint64_t* out_a, uint64_t* out_b, uint64_t count);
+/* out[0] = dependency levels, out[1] = bootstrapped gates, out[2] = kernel launches of the last circuit call */
+int luxb200_circuit_last_stats(luxb200_ctx* ctx, uint64_t* out);
 
 /* ---- integer-pipe roofline probe: measured IMAD-class issue rate of this GPU (ops/s) ------------------- */
 int luxb200_intpipe_probe(int device, double* imad_per_s, double* mixed_per_s);
