@@ -134,20 +134,22 @@ extern "C" int luxb200_circuit_batch(luxb200_ctx* c, uint32_t n_inputs, const lu
     // slots: inputs first, then each level's bootstrapped gates as one contiguous run (the key switch of the level writes
     // the run in place), NOT wires behind them
     std::vector<u32> slot(wires);
-    std::vector<u32> lv_first(depth + 2, 0), lv_cnt(depth + 2, 0);
+    std::vector<u32> lv_first(depth + 3, 0), lv_cnt(depth + 3, 0);
     for (u32 i = 0; i < n_inputs; ++i) slot[i] = i;
-    u32 next = n_inputs;
-    std::vector<u32> order;   // bootstrapped gates in level order
-    order.reserve(n_boot);
-    for (u32 lv = 1; lv <= depth; ++lv) {
-        lv_first[lv] = (u32)order.size();
-        for (u32 g = 0; g < n_gates; ++g)
-            if (gates[g].op != LUXB200_OP_NOT && level[n_inputs + g] == lv) {
-                slot[n_inputs + g] = next++;
-                order.push_back(g);
-            }
-        lv_cnt[lv] = (u32)order.size() - lv_first[lv];
+    std::vector<u32> order(n_boot);   // bootstrapped gates in level order (counting sort, stable in gate order)
+    for (u32 g = 0; g < n_gates; ++g)
+        if (gates[g].op != LUXB200_OP_NOT) lv_cnt[level[n_inputs + g]]++;
+    for (u32 lv = 1; lv <= depth; ++lv) lv_first[lv + 1] = lv_first[lv] + lv_cnt[lv];
+    {
+        std::vector<u32> fill(lv_first);
+        for (u32 g = 0; g < n_gates; ++g) {
+            if (gates[g].op == LUXB200_OP_NOT) continue;
+            const u32 k = fill[level[n_inputs + g]]++;
+            order[k]           = g;
+            slot[n_inputs + g] = n_inputs + k;
+        }
     }
+    u32 next = n_inputs + n_boot;
     for (u32 g = 0; g < n_gates; ++g)
         if (gates[g].op == LUXB200_OP_NOT) slot[n_inputs + g] = next++;
     const u32 q = (u32)c->p.q, n = c->p.n;
@@ -201,9 +203,11 @@ extern "C" int luxb200_circuit_batch(luxb200_ctx* c, uint32_t n_inputs, const lu
         LB_TRY(c->wb.ensure(cap * 4));
         LB_TRY(c->clsel.ensure(cap * 4));
     }
+    std::vector<std::vector<u32>> nots(depth + 1);   // NOT gates by level, in gate order (a NOT may feed a NOT)
+    for (u32 g = 0; g < n_gates; ++g)
+        if (gates[g].op == LUXB200_OP_NOT) nots[level[n_inputs + g]].push_back(g);
     auto run_nots = [&](u32 lv) -> int {
-        for (u32 g = 0; g < n_gates; ++g) {
-            if (gates[g].op != LUXB200_OP_NOT || level[n_inputs + g] != lv) continue;
+        for (u32 g : nots[lv]) {
             circuit_not_kernel<<<nblk(count * (n + 1), 256), 256, 0, c->stream>>>(
                 pool_a, pool_b, (u64)slot[gates[g].in0] * count, (u64)slot[n_inputs + g] * count, n, q, count);
             c->launches++;
