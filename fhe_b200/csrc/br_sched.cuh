@@ -107,7 +107,7 @@ __device__ __forceinline__ void mac_auto_split(u32 (&acc)[(1 << LOGN) / 32], con
 #pragma unroll
         for (int d = 0; d < ND; ++d) {
             k1[d] = __ldg(reinterpret_cast<const uint4*>(ak + (size_t)(d * 2 + c) * N) + v * 32 + lane);
-            if (d < LO || d >= HI) dx[d] = exch[d * (N / 4) + v * 32 + lane];
+            if (d < LO || d >= HI) dx[d] = exch[2 * d * (N / 4) + v * 32 + lane];   // warp 0 publishes digit d in row 2d
         }
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
@@ -125,11 +125,11 @@ __device__ __forceinline__ void mac_auto_split(u32 (&acc)[(1 << LOGN) / 32], con
 // in the same code window (instruction-cache sharing) and the exchange buffer is race-free.  A ciphertext whose
 // list is exhausted idles at the barriers until every list in the CTA is done (op counts differ by a few percent).
 template <int LOGN, int LOGH, int ROWS, int CTS>
-__global__ void __launch_bounds__(64 * CTS, 1)
+__global__ void __launch_bounds__(64 * CTS, CTS <= 3 ? 2 : 1)
 br_sched_kernel(const __grid_constant__ BrParams P) {
     using W         = WNtt<LOGN, LOGH>;
     using S         = BrSmem<LOGN, LOGH, ROWS, CTS>;
-    constexpr int N = W::N, E = W::E, ND = ROWS / 2, K0 = (ND + 1) / 2;
+    constexpr int N = W::N, E = W::E, ND = ROWS / 2;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     S& sm = *reinterpret_cast<S*>(smem_raw);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -170,59 +170,23 @@ br_sched_kernel(const __grid_constant__ BrParams P) {
         if (__syncthreads_and(done)) break;
         const u32 ty = done ? (u32)OP_END : (op & OP_MASK), arg = op & ~OP_MASK;
         u32 dg[ND][E];
-        if (ty == OP_EXT) {
-            digits_from_acc<LOGN, LOGH, ROWS>(acc, dg, P, scratch, sm.twB, sm.twiB, exch, c, lane);
-        } else if (ty == OP_PERM1) {
-            if (c == 1) permute_eval<LOGN, LOGH>(acc, scratch, P.automap + (size_t)arg * N, lane);
-        } else if (ty == OP_AUTO) {  // Automorphism(a = 5^arg or 2N-5), rgsw-acc-lmkcdey.cpp:257-287
-            // Only component 0 is key-switched, so its warp would run INTT + ND forward transforms while the partner
-            // idles.  The partner takes the upper digit polynomial instead: warp 0 hands it over in COEFFICIENT form
-            // through the exchange rows an automorphism round leaves unused (ND..), one warp-pair barrier in between.
+        if (ty == OP_AUTO || (ty == OP_PERM1 && c == 1))   // EVALUATION-format automorphism of the accumulator
             permute_eval<LOGN, LOGH>(acc, scratch, P.automap + (size_t)arg * N, lane);
-            uint4* raw = exch + ND * (N / 4);
-            if (c == 0) {
-                W::inverse(acc, P.C, scratch, sm.twiB, P.twifull, lane);  // cta -> COEFFICIENT, canonical
-#pragma unroll
-                for (int r = 0; r < E; ++r) {
-                    u32 d[ND];
-                    decompose_coeff<ND>(acc[r], P.C.Q, P.qhalf, (int)P.gbits, d);
-#pragma unroll
-                    for (int k = 0; k < ND; ++k) dg[k][r] = d[k];
-                }
-#pragma unroll
-                for (int k = K0; k < ND; ++k)
-#pragma unroll
-                    for (int v = 0; v < E / 4; ++v)
-                        raw[(k - K0) * (N / 4) + v * 32 + lane] =
-                            make_uint4(dg[k][4 * v], dg[k][4 * v + 1], dg[k][4 * v + 2], dg[k][4 * v + 3]);
-            }
-            pair_barrier(1 + slot);
-            if (c == 1) {
-#pragma unroll
-                for (int k = K0; k < ND; ++k)
-#pragma unroll
-                    for (int v = 0; v < E / 4; ++v) {
-                        const uint4 t = raw[(k - K0) * (N / 4) + v * 32 + lane];
-                        dg[k][4 * v] = t.x; dg[k][4 * v + 1] = t.y; dg[k][4 * v + 2] = t.z; dg[k][4 * v + 3] = t.w;
-                    }
-            }
-#pragma unroll
-            for (int k = 0; k < ND; ++k) {
-                if ((k < K0) != (c == 0)) continue;   // warp 0: digits < K0, warp 1: the rest
-                W::template forward<1>(dg[k], P.C, scratch, sm.twB, P.twfull, lane);
-                uint4* dst = exch + k * (N / 4);
-#pragma unroll
-                for (int v = 0; v < E / 4; ++v)
-                    dst[v * 32 + lane] = make_uint4(dg[k][4 * v], dg[k][4 * v + 1], dg[k][4 * v + 2], dg[k][4 * v + 3]);
-            }
-        }
+        // ONE inlined copy of the digit pipeline (INTT -> decompose -> NTTs -> publish rows 2k+c) for both op kinds, so all
+        // warps of the CTA walk the same instruction window: with a separate automorphism pipeline (warp 1 transforming
+        // the upper digit polynomial) the loop body was 15.7 k instructions and 27 % of the issue-stall samples were
+        // no_instructions (profiles/r1_sched_lmk_v0.txt; the L1.5 instruction cache holds 2 k instructions).
+        // External product: both warps.  Automorphism (rgsw-acc-lmkcdey.cpp:257-287): only component 0 is key-switched;
+        // warp 1 waits at the barrier and then adds sum_d digit_d * ak[d][1] from warp 0's published rows.
+        if (ty == OP_EXT || (ty == OP_AUTO && c == 0))
+            digits_from_acc<LOGN, LOGH, ROWS>(acc, dg, P, scratch, sm.twB, sm.twiB, exch, c, lane);
         __syncthreads();
         if (ty == OP_EXT) {
             mac_replace<LOGN, ROWS>(acc, dg, exch, P, P.bsk + (size_t)arg * kblock, c, lane);
         } else if (ty == OP_AUTO) {
             const u32* ak = P.bsk + P.auto_off + (size_t)arg * ablock;
-            if (c == 0) mac_auto_split<LOGN, ND, 0, K0, false>(acc, dg, exch, P, ak, 0, lane);
-            else        mac_auto_split<LOGN, ND, K0, ND, true>(acc, dg, exch, P, ak, 1, lane);
+            if (c == 0) mac_auto_split<LOGN, ND, 0, ND, false>(acc, dg, exch, P, ak, 0, lane);   // own digits, registers
+            else        mac_auto_split<LOGN, ND, 0, 0, true>(acc, dg, exch, P, ak, 1, lane);     // warp 0's rows 2d
         }
         if (!done) ++pc;
     }
