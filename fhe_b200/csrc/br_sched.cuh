@@ -133,7 +133,10 @@ br_sched_kernel(const __grid_constant__ BrParams P) {
     extern __shared__ __align__(16) unsigned char smem_raw[];
     S& sm = *reinterpret_cast<S*>(smem_raw);
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const int slot = warp >> 1, c = warp & 1;
+    // Warp w issues on SM sub-partition w % 4, so ciphertext slots 0, 2, 4 share sub-partitions {0, 1} and slots 1, 3, 5 share
+    // {2, 3}.  In an LMKCDEY automorphism round only component 0 runs the digit pipeline; with c = w & 1 every component-0
+    // warp would sit on sub-partitions 0 and 2.  Swapping the roles in every other slot pair spreads them 2 : 1.
+    const int slot = warp >> 1, c = (warp & 1) ^ ((slot >> 1) & 1);
     for (int i = threadIdx.x; i < W::NB * 32; i += blockDim.x) {
         sm.twB[i]  = P.twB[i];
         sm.twiB[i] = P.twiB[i];

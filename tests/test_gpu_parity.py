@@ -313,3 +313,31 @@ def test_external_product_and_device_memory(name, method, cnt):
     _l.check(L.luxb200_dev_mem_info(0, C.byref(f), C.byref(t)))
     assert t.value > 100e9 and f.value <= t.value
     ctx.close(); oc.close()
+
+
+def test_evalfunc_std128_lmkcdey_vs_oracle():
+    """EvalFunc on STD128_LMKCDEY (q = 2048 > N: periodic and negacyclic LUTs only, binfhe-base-scheme.cpp:264-332) through
+    the automorphism rounds of the scheduled kernel, bit for bit against the oracle; p = q / 256 = 8 like bench_extra."""
+    from fhe_b200.context import BinFHEContext
+    from fhe_b200 import keygen as kg
+    ctx = BinFHEContext().GenerateBinFHEContext("STD128_LMKCDEY", "LMKCDEY")
+    ks = kg.keygen(ctx, seed=77)
+    ctx.BTKeyLoad(ks.bsk, ks.kskA, ks.kskB)
+    oc = oracle_twin(ctx, "LMKCDEY")
+    oc.load(ks.bsk, ks.kskA, ks.kskB)
+    rng = np.random.default_rng(5)
+    p, cnt = 8, 6
+    m = rng.integers(0, p, cnt)
+    a, b = kg.encrypt(ctx, ks.sk, m, rng, p=p)
+    O = oracle()
+    for f in (lambda x, pp: x % (pp // 2), lambda x, pp: x + 1 if x < pp // 2 else pp - (x - pp // 2 + 1)):   # periodic; negacyclic (no zero:
+        # checkInputFunction compares lut[i] with q - lut[i + q/2] unreduced, binfhe-base-scheme.h:245-260)
+        lut = ctx.GenerateLUTviaFunction(f, p)
+        (oa, ob), res = ctx.EvalFuncBatch((a, b), lut)
+        assert res.success, res.error
+        lut64 = np.ascontiguousarray(lut, np.uint64)
+        xa = np.zeros((cnt, ctx.n), np.uint64); xb = np.zeros(cnt, np.uint64)
+        rc = O.orc_evalfunc(oc.h, P(a), P(b), P(lut64), len(lut64), ctx.GetBeta(), P(xa), P(xb), cnt, ctx.q, 4)
+        assert rc == 0
+        assert (oa == xa).all() and (ob == xb).all()
+    ctx.close(); oc.close()
