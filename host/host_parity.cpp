@@ -130,6 +130,8 @@ int main(int argc, char** argv) {
         for (size_t i = 0; i < cnt; ++i) cpu[i] = cc.EvalBinGate(CMUX, std::vector<LWECiphertext>{c1[i], c2[i], c3[i]});
         report("EvalCMUXBatch", cnt, count_diff(gpu, cpu));
     }
+    std::vector<NativeInteger> dag_lut;   // set when EvalFunc is available for this parameter set (q <= N)
+    int dag_p = 0;
     {
         // EvalFunc: p = GetMaxPlaintextSpace, f(m) = m^3 mod p  (the reference's eval-function example)
         const int p = cc.GetMaxPlaintextSpace().ConvertToInt();
@@ -152,6 +154,7 @@ int main(int argc, char** argv) {
             } else {
                 if (!r.success) { std::printf("EvalFuncBatch failed: %s\n", r.error.c_str()); return 2; }
                 report("EvalFuncBatch", cnt, count_diff(gpu, cpu));
+                dag_lut = lut; dag_p = p;
             }
         }
     }
@@ -173,6 +176,29 @@ int main(int argc, char** argv) {
         size_t bad = (!rg.success || !rc.success) ? 1 : 0;
         for (size_t i = 0; i < og.size() && !bad; ++i) bad += !same_ct(dg.GetResult(og[i]), dc.GetResult(oc[i]));
         report("BatchDAG_levels", og.size(), bad);
+    }
+
+    // ---- BatchDAG with an EvalFunc node: not a gate circuit, so Execute levels it on the host (one batched call per level
+    // and operation kind) — same results as the reference's sequential walk
+    if (!dag_lut.empty()) {
+        auto build = [&](BatchDAG& d, std::vector<size_t>& outs, const std::vector<LWECiphertext>& fin) {
+            for (size_t i = 0; i + 1 < cnt; i += 2) {
+                size_t a = d.AddCiphertext(c1[i]), b = d.AddCiphertext(c2[i + 1]), e = d.AddCiphertext(fin[i]);
+                size_t x = d.AddBinGate(NAND, a, b), f = d.AddEvalFunc(e, dag_lut), y = d.AddBinGate(XNOR, x, b);
+                size_t u = d.AddBootstrap(y);
+                outs.insert(outs.end(), {x, f, y, u});
+            }
+        };
+        std::vector<LWECiphertext> fin(cnt);
+        for (size_t i = 0; i < cnt; ++i) fin[i] = cc.Encrypt(sk, i % dag_p, LARGE_DIM, dag_p);
+        BatchDAG dg(cc), dc(cc);
+        std::vector<size_t> og, oc;
+        build(dg, og, fin); build(dc, oc, fin);
+        auto rg = dg.Execute(), rc = dc.Execute(BATCH_CPU_FORCE);
+        size_t bad = (!rg.success || !rc.success) ? 1 : 0;
+        if (bad) std::printf("BatchDAG_host_levels: %s | %s\n", rg.error.c_str(), rc.error.c_str());
+        for (size_t i = 0; i < og.size() && !bad; ++i) bad += !same_ct(dg.GetResult(og[i]), dc.GetResult(oc[i]));
+        report("BatchDAG_host_levels", og.size(), bad);
     }
 
     // ---- 8-bit comparison circuit (BASELINE config 4), levelled ------------------------------------------------
