@@ -15,6 +15,14 @@ def shard_range(count, rank, world):
     return lo, lo + base + (1 if rank < rem else 0)
 
 
+def shard_circuit_inputs(in_a, in_b, rank, world):
+    """A circuit batch (luxb200_circuit_batch) shards over its independent input sets: wire-major buffers in_a
+    [wires][count][n], in_b [wires][count] -> this rank's contiguous slice of the count axis (every rank keeps all wires
+    and the whole gate list; no exchange between ranks at any level)."""
+    lo, hi = shard_range(in_b.shape[1], rank, world)
+    return np.ascontiguousarray(in_a[:, lo:hi]), np.ascontiguousarray(in_b[:, lo:hi]), (lo, hi)
+
+
 def broadcast_keys(arrays, lengths, src=0, device="cpu"):
     """Broadcast the canonical flat key arrays from rank `src`.
 

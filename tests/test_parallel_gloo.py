@@ -22,6 +22,11 @@ def _worker(rank, world, port, q):
     lo, hi = par.shard_range(1001, rank, world)
     total = par.gather_counts(hi - lo)
     tmax = par.max_over_ranks(1.0 + rank)
+    # a circuit batch shards over its input sets (count axis), all wires on every rank
+    ia = np.arange(3 * 11 * 4, dtype=np.uint64).reshape(3, 11, 4); ib = np.arange(33, dtype=np.uint64).reshape(3, 11)
+    sa, sb, (clo, chi) = par.shard_circuit_inputs(ia, ib, rank, world)
+    assert sa.shape == (3, chi - clo, 4) and (sa == ia[:, clo:chi]).all() and (sb == ib[:, clo:chi]).all()
+    assert par.gather_counts(chi - clo) == 11
     q.put((rank, chk, lo, hi, total, tmax))
     dist.destroy_process_group()
 
