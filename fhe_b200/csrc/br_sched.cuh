@@ -166,10 +166,14 @@ br_sched_kernel(const __grid_constant__ BrParams P) {
     const size_t ablock = (size_t)ND * 2 * N;
     bool done = !live;
     u32 pc    = 0;
+    // the op word of the NEXT round is fetched a round ahead, so no round starts by waiting on a global load
+    // (lists end with OP_END: pc + 1 is readable whenever the current op is not the end)
+    u32 op_next = done ? (u32)OP_END : ops[0];
 #pragma unroll 1
     for (;;) {
-        u32 op = done ? (u32)OP_END : ops[pc];
+        const u32 op = op_next;
         if ((op & OP_MASK) == OP_END) done = true;
+        op_next = done ? (u32)OP_END : ops[pc + 1];
         if (__syncthreads_and(done)) break;
         const u32 ty = done ? (u32)OP_END : (op & OP_MASK), arg = op & ~OP_MASK;
         u32 dg[ND][E];
