@@ -120,10 +120,11 @@ class BinFHEContext:
                                                     _l.ptr(ob), cnt, p)
         return (oa, ob), self._result(rc, cnt)
 
-    def EvalCMUXBatch(self, ct_true, ct_false, ct_sel):
-        """EvalCMUXBatch(sel, ct_true, ct_false) of binfhe-batch.h:113-125 = EvalBinGate(CMUX, {ct1, ct2, sel})."""
-        a = np.stack([self._u64(ct_true[0]), self._u64(ct_false[0]), self._u64(ct_sel[0])], axis=1)
-        b = np.stack([self._u64(ct_true[1]), self._u64(ct_false[1]), self._u64(ct_sel[1])], axis=1)
+    def EvalCMUXBatch(self, ct_sel, ct_true, ct_false):
+        """lux::fhe::EvalCMUXBatch(cc, ct_sel, ct_true, ct_false, ...) (binfhe-batch.h:113-125): per element
+        EvalBinGate(CMUX, {sel, true, false}) — the vector order of batch.cpp:231-239, which host/batch_b200.cpp keeps too."""
+        a = np.stack([self._u64(ct_sel[0]), self._u64(ct_true[0]), self._u64(ct_false[0])], axis=1)
+        b = np.stack([self._u64(ct_sel[1]), self._u64(ct_true[1]), self._u64(ct_false[1])], axis=1)
         return self.EvalBinGateMultiBatch("CMUX", a, b)
 
     def BootstrapBatch(self, ct, p=4, extended=False):

@@ -1,4 +1,6 @@
 // api.cu — C ABI of libluxb200.so (see include/luxb200.h for the reference interfaces each entry replaces).
+#include <algorithm>
+
 #include "api_common.h"
 #include "aux_kernels.cuh"
 #include "br_sched.cuh"
@@ -114,7 +116,7 @@ int luxb200_ctx_create(const luxb200_params* p, int device, luxb200_ctx** out) {
     c->digitsR = digit_count(p->q, p->baseR ? p->baseR : 2);
     c->rows = 2 * (c->digitsG - 1);
     if (c->p.psi == 0) c->p.psi = root_of_unity(2ull * p->N, p->Q);
-    if (c->rows != 4 && c->rows != 6 && c->rows != 2) { delete c; return lb_fail(LUXB200_ERR_UNSUPPORTED, "digitsG-1 = %u not supported", c->rows / 2); }
+    if (c->rows != 4 && c->rows != 6 && c->rows != 2) { luxb200_ctx_destroy(c); return lb_fail(LUXB200_ERR_UNSUPPORTED, "digitsG-1 = %u not supported", c->rows / 2); }
     // reduce64 constants: x < max(rows * 2Q * Q, 8 Q^2 + 4Q)
     {
         u128_t Q = p->Q, xmax = (u128_t)c->rows * 2 * Q * Q;
@@ -123,15 +125,15 @@ int luxb200_ctx_create(const luxb200_params* p, int device, luxb200_ctx** out) {
         uint32_t b = 0;
         while ((xmax >> b) != 0) ++b;
         uint32_t s = b > 32 ? b - 32 : 0;
-        if (s > bits_of(p->Q) - 1) { delete c; return lb_fail(LUXB200_ERR_UNSUPPORTED, "Q too large for the 64->32 reduction (rows=%u)", c->rows); }
+        if (s > bits_of(p->Q) - 1) { luxb200_ctx_destroy(c); return lb_fail(LUXB200_ERR_UNSUPPORTED, "Q too large for the 64->32 reduction (rows=%u)", c->rows); }
         c->red_s = s;
         c->red_mu = (uint32_t)((((u128_t)1) << (s + 32)) / Q);
     }
     int rc = c->ntt.build(p->N, p->Q, c->p.psi);
-    if (rc) { delete c; return rc; }
+    if (rc) { luxb200_ctx_destroy(c); return rc; }
     cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
     for (int i = 0; i < 5 && e == cudaSuccess; ++i) e = cudaEventCreate(&c->ev[i]);
-    if (e != cudaSuccess) { delete c; return lb_fail(LUXB200_ERR_CUDA, "stream/event creation failed: %s", cudaGetErrorString(e)); }
+    if (e != cudaSuccess) { luxb200_ctx_destroy(c); return lb_fail(LUXB200_ERR_CUDA, "stream/event creation failed: %s", cudaGetErrorString(e)); }
     if (p->method == LUXB200_GINX) {
         // monomials X^a - 1 in EVALUATION format (rgsw-cryptoparameters.cpp:96-113), sigma order:
         // value at index p is psi^(a (2 brv(p) + 1)) - 1
@@ -198,7 +200,8 @@ void luxb200_ctx_destroy(luxb200_ctx* c) {
     cudaSetDevice(c->device);
     DevBuf* bufs[] = {&c->bsk, &c->mono, &c->kskA, &c->kskB, &c->automap, &c->loggen, &c->in0, &c->in1, &c->in2, &c->in3, &c->wa,
                       &c->wb, &c->lut, &c->ext, &c->oa, &c->ob, &c->o64a, &c->o64b, &c->sched, &c->tmpa, &c->tmpb,
-                      &c->tmpc, &c->tmpd, &c->cpa, &c->cpb, &c->cdesc, &c->clsel};
+                      &c->tmpc, &c->tmpd, &c->cpa, &c->cpb, &c->cdesc, &c->clsel, &c->cx1a, &c->cx1b, &c->cx2a, &c->cx2b,
+                      &c->xin};
     for (DevBuf* b : bufs) b->release();
     c->ntt.release();
     for (int s = 0; s < 2; ++s) {
@@ -238,6 +241,7 @@ uint64_t luxb200_ksk_len(luxb200_ctx* c) {
 
 int luxb200_load_bsk(luxb200_ctx* c, const uint64_t* bsk, int on_device) {
     if (!c || !bsk) return lb_fail(LUXB200_ERR_INVALID_ARG, "null argument");
+    LB_LOCK(c);
     LB_TRY(lb_set_device(c->device));
     const uint64_t len = luxb200_bsk_len(c);
     LB_TRY(c->bsk.ensure(len * 4));
@@ -263,6 +267,7 @@ int luxb200_load_bsk(luxb200_ctx* c, const uint64_t* bsk, int on_device) {
 
 int luxb200_load_ksk(luxb200_ctx* c, const uint64_t* A, const uint64_t* B, int on_device) {
     if (!c || !A || !B) return lb_fail(LUXB200_ERR_INVALID_ARG, "null argument");
+    LB_LOCK(c);
     LB_TRY(lb_set_device(c->device));
     const uint64_t rows = (uint64_t)c->p.N * c->p.baseKS * c->digitsKS;
     LB_TRY(c->kskA.ensure(rows * c->npad * c->ks_elem));
@@ -305,8 +310,85 @@ int luxb200_load_ksk(luxb200_ctx* c, const uint64_t* A, const uint64_t* B, int o
 
 int luxb200_synchronize(luxb200_ctx* c) {
     if (!c) return lb_fail(LUXB200_ERR_INVALID_ARG, "null argument");
+    LB_LOCK(c);
     LB_TRY(lb_set_device(c->device));
     LB_CUDA(cudaStreamSynchronize(c->stream));
+    return 0;
+}
+
+
+// ---- pinned host staging (cudaHostAlloc): host-side packers write ciphertext batches straight into page-locked memory so
+// the copy-in / copy-out streams of the batch pipeline run at PCIe speed and truly overlap the kernels
+int luxb200_host_alloc(uint64_t bytes, void** out) {
+    if (!out) return lb_fail(LUXB200_ERR_INVALID_ARG, "null argument");
+    *out = nullptr;
+    int cnt = 0;
+    if (cudaGetDeviceCount(&cnt) != cudaSuccess || cnt == 0)
+        return lb_fail(LUXB200_ERR_NO_DEVICE, "no CUDA device available; libluxb200 has no CPU fallback");
+    if (cudaHostAlloc(out, bytes ? bytes : 1, cudaHostAllocPortable) != cudaSuccess) {
+        cudaGetLastError();
+        return lb_fail(LUXB200_ERR_ALLOC, "cudaHostAlloc(%llu) failed", (unsigned long long)bytes);
+    }
+    return 0;
+}
+int luxb200_host_free(void* p) {
+    if (!p) return 0;
+    LB_CUDA(cudaFreeHost(p));
+    return 0;
+}
+
+// ---- one-time key broadcast inside one process: ctxs[0] holds the keys (luxb200_load_bsk / _ksk); every other context
+// (same parameters, another GPU of the box) receives the PACKED device images — u32 sigma-ordered BSK, u16/u32 KSK rows,
+// u32 KSK B — by peer-to-peer copies over NVLink/NVSwitch (cudaMemcpyPeerAsync; staged through the host by the driver
+// when two devices have no peer path).  Doubling tree: after round r, 2^r contexts hold the keys and each sends to one
+// more, so all egress links work and n devices take ceil(log2 n) rounds.  No collective exists on the per-gate path.
+int luxb200_broadcast_keys(luxb200_ctx* const* ctxs, int n) {
+    if (!ctxs || n <= 0) return lb_fail(LUXB200_ERR_INVALID_ARG, "null argument");
+    luxb200_ctx* r = ctxs[0];
+    if (!r) return lb_fail(LUXB200_ERR_INVALID_ARG, "null context");
+    if (!r->have_bsk && !r->have_ksk) return lb_fail(LUXB200_ERR_NO_KEYS, "luxb200_broadcast_keys: the root context holds no keys");
+    for (int i = 1; i < n; ++i) {
+        luxb200_ctx* c = ctxs[i];
+        if (!c) return lb_fail(LUXB200_ERR_INVALID_ARG, "null context");
+        if (memcmp(&c->p, &r->p, sizeof(luxb200_params)) != 0)
+            return lb_fail(LUXB200_ERR_INVALID_ARG, "luxb200_broadcast_keys: context %d has different parameters", i);
+        for (int j = 0; j < i; ++j)
+            if (ctxs[j] == c) return lb_fail(LUXB200_ERR_INVALID_ARG, "luxb200_broadcast_keys: context %d listed twice", i);
+    }
+    // whichever of the two keys the root holds is sent (a backend may bind a refresh key before a switching key exists)
+    const size_t bsk_bytes = r->have_bsk ? luxb200_bsk_len(r) * 4 : 0;
+    const size_t rowsK = (size_t)r->p.N * r->p.baseKS * r->digitsKS;
+    const size_t ka_bytes = r->have_ksk ? rowsK * r->npad * r->ks_elem : 0, kb_bytes = r->have_ksk ? rowsK * 4 : 0;
+    for (int i = 1; i < n; ++i) {
+        luxb200_ctx* c = ctxs[i];
+        LB_TRY(lb_set_device(c->device));
+        if (bsk_bytes) LB_TRY(c->bsk.ensure(bsk_bytes));
+        if (ka_bytes) { LB_TRY(c->kskA.ensure(ka_bytes)); LB_TRY(c->kskB.ensure(kb_bytes)); }
+        if (c->device != r->device) {
+            int can = 0;
+            cudaDeviceCanAccessPeer(&can, c->device, r->device);
+            if (can && cudaDeviceEnablePeerAccess(r->device, 0) == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+        }
+    }
+    for (int have = 1; have < n; have *= 2) {
+        const int m = std::min(have, n - have);
+        for (int k = 0; k < m; ++k) {   // ctxs[k] -> ctxs[have + k], on the receiver's stream
+            luxb200_ctx *src = ctxs[k], *dst = ctxs[have + k];
+            LB_TRY(lb_set_device(dst->device));
+            if (bsk_bytes) LB_CUDA(cudaMemcpyPeerAsync(dst->bsk.p, dst->device, src->bsk.p, src->device, bsk_bytes, dst->stream));
+            if (ka_bytes) {
+                LB_CUDA(cudaMemcpyPeerAsync(dst->kskA.p, dst->device, src->kskA.p, src->device, ka_bytes, dst->stream));
+                LB_CUDA(cudaMemcpyPeerAsync(dst->kskB.p, dst->device, src->kskB.p, src->device, kb_bytes, dst->stream));
+            }
+        }
+        for (int k = 0; k < m; ++k) {
+            luxb200_ctx* dst = ctxs[have + k];
+            LB_TRY(lb_set_device(dst->device));
+            LB_CUDA(cudaStreamSynchronize(dst->stream));
+            dst->have_bsk = r->have_bsk;
+            dst->have_ksk = r->have_ksk;
+        }
+    }
     return 0;
 }
 

@@ -5,6 +5,7 @@
 #include <cstdarg>
 #include <cstdio>
 #include <cstring>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -29,10 +30,19 @@ int lb_fail(int code, const char* fmt, ...);
         if (r_ != 0) return r_; \
     } while (0)
 
-// grow-only device buffer
+// grow-only device buffer; owns its allocation (freed on destruction, so early error returns do not leak)
 struct DevBuf {
     void* p = nullptr;
     size_t cap = 0;
+    DevBuf() = default;
+    DevBuf(const DevBuf&) = delete;
+    DevBuf& operator=(const DevBuf&) = delete;
+    DevBuf(DevBuf&& o) noexcept : p(o.p), cap(o.cap) { o.p = nullptr; o.cap = 0; }
+    DevBuf& operator=(DevBuf&& o) noexcept {
+        if (this != &o) { release(); p = o.p; cap = o.cap; o.p = nullptr; o.cap = 0; }
+        return *this;
+    }
+    ~DevBuf() { release(); }
     int ensure(size_t bytes) {
         if (bytes <= cap) return 0;
         if (p) cudaFree(p);
@@ -63,6 +73,10 @@ struct Ntt32Tables {
 };
 
 struct luxb200_ctx {
+    // One context = one device, one stream, one set of work buffers: the entry points serialise on this mutex, so several
+    // host threads (the reference's std::async batch futures, batch.cpp:320-349) may share a context safely; calls on
+    // DIFFERENT contexts run concurrently.
+    std::recursive_mutex mu;
     luxb200_params p;
     int device = 0;
     uint32_t digitsG = 0, digitsKS = 0, digitsR = 0, rows = 0, logN = 0;
@@ -76,6 +90,8 @@ struct luxb200_ctx {
     bool have_bsk = false, have_ksk = false;
     // work buffers
     DevBuf in0, in1, in2, in3, wa, wb, lut, ext, oa, ob, o64a, o64b, sched, tmpa, tmpb, tmpc, tmpd;
+    DevBuf cx1a, cx1b, cx2a, cx2b;   // CMUX intermediates (two NAND results), kept so the call does no cudaMalloc/cudaFree
+    DevBuf xin;                      // extended (N, Q) inputs packed [count][N+1] before SwitchCTtoqn
     DevBuf cpa, cpb, cdesc, clsel;   // gate circuits (circuit.cu): wire pool (a, b), gate descriptors, per-item table offsets
     uint64_t launches = 0;
     float t_prep = 0, t_br = 0, t_ks = 0, t_total = 0;
@@ -93,6 +109,7 @@ struct luxb200_ctx {
 };
 
 int lb_set_device(int device);
+#define LB_LOCK(c) std::lock_guard<std::recursive_mutex> lb_guard_((c)->mu)
 
 // ---- entry points of api.cu used by circuit.cu (a separate translation unit, same library) -------------------
 // test-vector table of a 2-input gate for plaintext modulus p (binfhe-base-scheme.cpp:535-567)

@@ -96,6 +96,7 @@ extern "C" int luxb200_circuit_batch(luxb200_ctx* c, uint32_t n_inputs, const lu
                                      uint64_t* out_a, uint64_t* out_b, uint64_t count) {
     if (!c || !in_a || !in_b || (n_gates && !gates) || (n_outputs && (!outputs || !out_a || !out_b)))
         return lb_fail(LUXB200_ERR_INVALID_ARG, "null argument");
+    LB_LOCK(c);
     if (n_inputs == 0) return lb_fail(LUXB200_ERR_INVALID_ARG, "a circuit needs at least one input wire");
     const u64 wires = (u64)n_inputs + n_gates;
     if (wires >= 0xffffffffull) return lb_fail(LUXB200_ERR_INVALID_ARG, "too many wires");
@@ -247,6 +248,7 @@ extern "C" int luxb200_circuit_batch(luxb200_ctx* c, uint32_t n_inputs, const lu
 
 extern "C" int luxb200_circuit_last_stats(luxb200_ctx* c, uint64_t* out) {
     if (!c || !out) return lb_fail(LUXB200_ERR_INVALID_ARG, "null argument");
+    LB_LOCK(c);
     out[0] = c->circ_stats[0]; out[1] = c->circ_stats[1]; out[2] = c->circ_stats[2];
     return 0;
 }

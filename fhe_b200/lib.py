@@ -45,6 +45,11 @@ SIGNATURES = {
     "luxb200_load_ksk": (INT, [VP, VP, VP, INT]),
     "luxb200_synchronize": (INT, [VP]),
     "luxb200_evalbingate_batch": (INT, [VP, INT, VP, VP, VP, VP, VP, VP, U64, INT]),
+    "luxb200_evalbingate_batch_ex": (INT, [VP, INT, VP, VP, VP, VP, VP, VP, U64, INT, U64, INT]),
+    "luxb200_switch_to_qn_batch": (INT, [VP, VP, VP, VP, VP, U64]),
+    "luxb200_broadcast_keys": (INT, [VP, INT]),
+    "luxb200_host_alloc": (INT, [U64, C.POINTER(VP)]),
+    "luxb200_host_free": (INT, [VP]),
     "luxb200_evalbingate_multi_batch": (INT, [VP, INT, U32, VP, VP, VP, VP, U64, U64]),
     "luxb200_bootstrap_batch": (INT, [VP, VP, VP, VP, VP, U64, U64, INT]),
     "luxb200_evalfunc_batch": (INT, [VP, VP, VP, VP, U64, U64, VP, VP, U64, U64]),

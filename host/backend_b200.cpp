@@ -2,8 +2,12 @@
 #include "backend_b200.h"
 #include "packed_b200.h"
 
+#include <atomic>
+#include <chrono>
 #include <cstring>
+#include <map>
 #include <stdexcept>
+#include <thread>
 
 namespace lux::fhe {
 namespace backend {
@@ -12,28 +16,52 @@ namespace {
 
 inline uint64_t u64(const NativeInteger& v) { return v.ConvertToInt<uint64_t>(); }
 
-// [count][len] a-parts and [count] b-parts of a batch of LWE ciphertexts (NativeVector storage is uint64 residues)
+static_assert(sizeof(NativeInteger) == sizeof(uint64_t), "NativeVector storage is one uint64 residue per element");
+
+// [count][len] a-parts and [count] b-parts of a batch of LWE ciphertexts, written to caller-provided (page-locked) arrays.
+// NativeVector storage is contiguous uint64 residues, so a row is one memcpy; rows are packed by all host threads.
+// Every element is checked: non-null, dimension `len`, modulus `mod` (0 = do not check).
+void flatten_cts_to(const LWECiphertext* cts, size_t count, uint32_t len, uint64_t mod, uint64_t* a, uint64_t* b) {
+    std::atomic<long> bad{-1};
+#pragma omp parallel for schedule(static)
+    for (size_t i = 0; i < count; ++i) {
+        const LWECiphertext& ct = cts[i];
+        if (!ct || ct->GetLength() != len || (mod && u64(ct->GetModulus()) != mod)) {
+            bad.store(static_cast<long>(i));
+            continue;
+        }
+        const NativeVector& v = ct->GetA();
+        std::memcpy(a + i * size_t(len), &v[0], size_t(len) * 8);
+        b[i] = u64(ct->GetB());
+    }
+    if (bad.load() >= 0)
+        throw std::invalid_argument("BackendB200: ciphertext " + std::to_string(bad.load()) +
+                                    " is empty or has the wrong dimension / modulus for this operation");
+}
 void flatten_cts(const std::vector<LWECiphertext>& cts, uint32_t len, std::vector<uint64_t>& a, std::vector<uint64_t>& b) {
     a.resize(cts.size() * size_t(len));
     b.resize(cts.size());
-    for (size_t i = 0; i < cts.size(); ++i) {
-        if (!cts[i] || cts[i]->GetLength() != len)
-            throw std::invalid_argument("BackendB200: ciphertext " + std::to_string(i) + " has the wrong dimension");
-        const NativeVector& v = cts[i]->GetA();
-        for (uint32_t k = 0; k < len; ++k) a[i * len + k] = u64(v[k]);
-        b[i] = u64(cts[i]->GetB());
-    }
+    flatten_cts_to(cts.data(), cts.size(), len, 0, a.data(), b.data());
 }
 
-void build_cts(const std::vector<uint64_t>& a, const std::vector<uint64_t>& b, uint32_t len, const NativeInteger& mod,
-               const NativeInteger& pmod, std::vector<LWECiphertext>& out) {
-    out.resize(b.size());
-    for (size_t i = 0; i < b.size(); ++i) {
+void build_cts_from(const uint64_t* a, const uint64_t* b, size_t count, uint32_t len, const NativeInteger& mod,
+                    const NativeInteger& pmod, LWECiphertext* out) {
+#pragma omp parallel for schedule(static)
+    for (size_t i = 0; i < count; ++i) {
         NativeVector v(len, mod);
-        for (uint32_t k = 0; k < len; ++k) v[k] = NativeInteger(a[i * len + k]);
+        std::memcpy(&v[0], a + i * size_t(len), size_t(len) * 8);
         out[i] = std::make_shared<LWECiphertextImpl>(std::move(v), NativeInteger(b[i]));
         out[i]->SetptModulus(pmod);
     }
+}
+void build_cts(const std::vector<uint64_t>& a, const std::vector<uint64_t>& b, uint32_t len, const NativeInteger& mod,
+               const NativeInteger& pmod, std::vector<LWECiphertext>& out) {
+    out.resize(b.size());
+    build_cts_from(a.data(), b.data(), b.size(), len, mod, pmod, out.data());
+}
+
+double now_ms() {
+    return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
 }
 
 void flatten_rlwe(const RLWECiphertext& ct, uint32_t N, uint64_t* out) {
@@ -48,24 +76,58 @@ void flatten_rlwe(const RLWECiphertext& ct, uint32_t N, uint64_t* out) {
 
 }  // namespace
 
-BackendB200::BackendB200(int device) : device_(device) {}
+BackendB200::BackendB200(int device) : devices_{device} {}
+BackendB200::BackendB200(std::vector<int> devices) : devices_(std::move(devices)) {
+    if (devices_.empty())
+        for (int d = 0; d < luxb200_device_count(); ++d) devices_.push_back(d);
+    if (devices_.empty()) devices_.push_back(0);
+}
+
+void BackendB200::destroy_contexts() {
+    for (luxb200_ctx* h : hs_)
+        if (h) luxb200_ctx_destroy(h);
+    hs_.clear();
+    h_ = nullptr;
+}
 
 BackendB200::~BackendB200() {
-    if (h_) luxb200_ctx_destroy(h_);
+    destroy_contexts();
+    for (Pinned& b : st_) b.release();
+}
+
+uint64_t* BackendB200::Pinned::ensure(size_t elems) {
+    if (elems <= cap) return p;
+    release();
+    void* q = nullptr;
+    if (luxb200_host_alloc(std::max<size_t>(elems, 1) * 8, &q) != LUXB200_OK)
+        throw std::runtime_error(std::string("BackendB200: pinned staging allocation failed: ") + luxb200_last_error());
+    p = static_cast<uint64_t*>(q);
+    cap = elems;
+    return p;
+}
+void BackendB200::Pinned::release() {
+    if (p) luxb200_host_free(p);
+    p = nullptr;
+    cap = 0;
 }
 
 void BackendB200::check(int rc, const char* what) const {
     if (rc != LUXB200_OK) throw std::runtime_error(std::string("BackendB200::") + what + ": " + luxb200_last_error());
 }
 
-bool BackendB200::IsAvailable() const { return luxb200_device_count() > device_; }
+bool BackendB200::IsAvailable() const {
+    const int cnt = luxb200_device_count();
+    for (int d : devices_)
+        if (d < 0 || d >= cnt) return false;
+    return true;
+}
 
 size_t BackendB200::DeviceMemory() const {
     uint64_t f = 0, t = 0;
-    return luxb200_dev_mem_info(device_, &f, &t) == LUXB200_OK ? size_t(t) : 0;
+    return luxb200_dev_mem_info(devices_[0], &f, &t) == LUXB200_OK ? size_t(t) : 0;
 }
 
-void BackendB200::Bind(BinFHEContext& cc) {
+static luxb200_params params_of(BinFHEContext& cc) {
     auto lwe = cc.GetParams()->GetLWEParams();
     auto rg  = cc.GetParams()->GetRingGSWParams();
     luxb200_params p{};
@@ -74,14 +136,37 @@ void BackendB200::Bind(BinFHEContext& cc) {
     p.baseKS = u64(lwe->GetBaseKS()); p.baseG = rg->GetBaseG(); p.baseR = rg->GetBaseR();
     p.numAutoKeys = rg->GetNumAutoKeys(); p.method = static_cast<uint32_t>(rg->GetMethod());
     p.psi = u64(rg->GetPolyParams()->GetRootOfUnity());
-    if (h_) { luxb200_ctx_destroy(h_); h_ = nullptr; }
-    check(luxb200_ctx_create(&p, device_, &h_), "Bind");
+    return p;
+}
+
+void BackendB200::Bind(BinFHEContext& cc) {
+    std::lock_guard<std::recursive_mutex> lk(mu_);
+    auto rg = cc.GetParams()->GetRingGSWParams();
+    const luxb200_params p = params_of(cc);
+    destroy_contexts();
+    hs_.assign(devices_.size(), nullptr);
+    for (size_t d = 0; d < devices_.size(); ++d) check(luxb200_ctx_create(&p, devices_[d], &hs_[d]), "Bind");
+    h_ = hs_[0];
     p_ = p;
     digitsG_ = rg->GetDigitsG(); digitsR_ = static_cast<uint32_t>(rg->GetDigitsR().size());
     rows_ = 2 * (digitsG_ - 1);
     poly_params_ = rg->GetPolyParams();
-    bound_bsk_ = bound_ksk_ = nullptr;
+    bound_bsk_.reset(); bound_ksk_.reset();
+    packed_bsk_ = packed_ksk_ = false;
     if (cc.GetRefreshKey() && cc.GetSwitchKey()) load_keys(cc.GetRefreshKey(), cc.GetSwitchKey());
+}
+
+void BackendB200::Attach(BinFHEContext& cc) {
+    std::lock_guard<std::recursive_mutex> lk(mu_);
+    if (!cc.GetParams()) throw std::invalid_argument("BinFHECryptoParams is empty");
+    const luxb200_params p = params_of(cc);
+    if (!h_ || std::memcmp(&p, &p_, sizeof(p)) != 0) {
+        Bind(cc);   // another parameter set (a second BinFHEContext): new device contexts, keys reloaded below
+        return;
+    }
+    // a context that holds keys must see exactly those on the device; one without keys keeps LoadPacked keys
+    if (cc.GetRefreshKey()) ensure_bsk(cc.GetRefreshKey());
+    if (cc.GetSwitchKey()) ensure_ksk(cc.GetSwitchKey());
 }
 
 // RingGSWACCKeyImpl -> canonical flat layout of include/luxb200.h (the orders of rgsw-acc-cggi.cpp:39-57,
@@ -89,12 +174,13 @@ void BackendB200::Bind(BinFHEContext& cc) {
 void BackendB200::flatten_bsk(const RingGSWACCKeyImpl& ek, std::vector<uint64_t>& out) const {
     out.assign(luxb200_bsk_len(h_), 0);
     const uint32_t N = p_.N, n = p_.n;
+    // slot list first, then all host threads copy polynomials (a 1 GB key for STD128_AP)
+    std::vector<std::pair<const RingGSWEvalKeyImpl*, size_t>> slots;
     size_t pos = 0;
     auto put = [&](const RingGSWEvalKey& k) {
         if (!k) throw std::invalid_argument("BackendB200: refresh key has an empty entry where one is required");
-        for (const auto& row : k->GetElements())
-            for (const auto& poly : row)
-                for (uint32_t t = 0; t < N; ++t) out[pos++] = u64(poly[t]);
+        slots.emplace_back(k.get(), pos);
+        for (const auto& row : k->GetElements()) pos += row.size() * size_t(N);
     };
     switch (p_.method) {
         case LUXB200_GINX:
@@ -113,20 +199,38 @@ void BackendB200::flatten_bsk(const RingGSWACCKeyImpl& ek, std::vector<uint64_t>
             for (uint32_t t = 0; t <= p_.numAutoKeys; ++t) put(ek[0][1][t]);
     }
     if (pos != out.size()) throw std::logic_error("BackendB200: refresh key does not match the parameter set");
+#pragma omp parallel for schedule(dynamic, 16)
+    for (size_t s = 0; s < slots.size(); ++s) {
+        size_t o = slots[s].second;
+        for (const auto& row : slots[s].first->GetElements())
+            for (const auto& poly : row) {
+                std::memcpy(&out[o], &poly.GetValues()[0], size_t(N) * 8);
+                o += N;
+            }
+    }
+}
+
+// every device holds the keys of device 0 (peer-to-peer over NVLink, luxb200_broadcast_keys)
+void BackendB200::share_keys() {
+    if (hs_.size() > 1) check(luxb200_broadcast_keys(hs_.data(), static_cast<int>(hs_.size())), "broadcast_keys");
 }
 
 void BackendB200::ensure_bsk(const RingGSWACCKey& ek) {
     if (!ek) throw std::invalid_argument("Bootstrapping keys have not been generated. Please call BTKeyGen before calling bootstrapping.");
-    if (ek.get() == bound_bsk_) return;
+    std::lock_guard<std::recursive_mutex> lk(mu_);
+    if (!packed_bsk_ && ek == bound_bsk_) return;   // the held shared_ptr pins the address: identity cannot be recycled
     std::vector<uint64_t> flat;
     flatten_bsk(*ek, flat);
     check(luxb200_load_bsk(h_, flat.data(), 0), "load_bsk");
-    bound_bsk_ = ek.get();
+    bound_bsk_ = ek;
+    packed_bsk_ = false;
+    share_keys();
 }
 
 void BackendB200::ensure_ksk(const LWESwitchingKey& ks) {
     if (!ks) throw std::invalid_argument("BackendB200: switching key is empty");
-    if (ks.get() == bound_ksk_) return;
+    std::lock_guard<std::recursive_mutex> lk(mu_);
+    if (!packed_ksk_ && ks == bound_ksk_) return;
     const auto& kA = ks->GetElementsA();
     const auto& kB = ks->GetElementsB();
     std::vector<uint64_t> A(luxb200_ksk_len(h_)), B(A.size() / p_.n);
@@ -137,11 +241,14 @@ void BackendB200::ensure_ksk(const LWESwitchingKey& ks) {
                 const NativeVector& v = kA[i][j][k];
                 if (pa + v.GetLength() > A.size() || pb >= B.size())
                     throw std::logic_error("BackendB200: switching key does not match the parameter set");
-                for (uint32_t t = 0; t < v.GetLength(); ++t) A[pa++] = u64(v[t]);
+                std::memcpy(&A[pa], &v[0], size_t(v.GetLength()) * 8);
+                pa += v.GetLength();
                 B[pb++] = u64(kB[i][j][k]);
             }
     check(luxb200_load_ksk(h_, A.data(), B.data(), 0), "load_ksk");
-    bound_ksk_ = ks.get();
+    bound_ksk_ = ks;
+    packed_ksk_ = false;
+    share_keys();
 }
 
 void BackendB200::load_keys(const RingGSWACCKey& ek, const LWESwitchingKey& ks) {
@@ -149,28 +256,45 @@ void BackendB200::load_keys(const RingGSWACCKey& ek, const LWESwitchingKey& ks) 
     ensure_ksk(ks);
 }
 
+void BackendB200::run_split(size_t count, const std::function<void(size_t, size_t, size_t)>& body) {
+    const size_t G = std::min(hs_.size(), std::max<size_t>(count, 1));
+    if (G <= 1) { body(0, 0, count); return; }
+    std::vector<std::thread> th;
+    std::vector<std::exception_ptr> err(G);
+    const size_t base = count / G, rem = count % G;
+    for (size_t d = 0; d < G; ++d) {
+        const size_t lo = d * base + std::min(d, rem), hi = lo + base + (d < rem ? 1 : 0);
+        th.emplace_back([&, d, lo, hi] {
+            try { if (hi > lo) body(d, lo, hi); } catch (...) { err[d] = std::current_exception(); }
+        });
+    }
+    for (auto& t : th) t.join();
+    for (auto& e : err)
+        if (e) std::rethrow_exception(e);
+}
+
 // ---- memory (backend.h:88-113) ----------------------------------------------------------------------------
 DeviceBuffer BackendB200::Allocate(size_t bytes) {
     DeviceBuffer b;
     void* p = nullptr;
-    check(luxb200_dev_alloc(device_, bytes, &p), "Allocate");
+    check(luxb200_dev_alloc(devices_[0], bytes, &p), "Allocate");
     b.ptr = p; b.size = bytes; b.device = BackendType::CUDA;
     return b;
 }
 void BackendB200::Free(DeviceBuffer& buffer) {
-    if (buffer.ptr) check(luxb200_dev_free(device_, buffer.ptr), "Free");
+    if (buffer.ptr) check(luxb200_dev_free(devices_[0], buffer.ptr), "Free");
     buffer.ptr = nullptr; buffer.size = 0;
 }
 void BackendB200::CopyToDevice(const void* host_ptr, DeviceBuffer& device_buffer, size_t bytes) {
     if (bytes > device_buffer.size) throw std::invalid_argument("BackendB200::CopyToDevice: buffer too small");
-    check(luxb200_dev_copy(device_, device_buffer.ptr, host_ptr, bytes, 1), "CopyToDevice");
+    check(luxb200_dev_copy(devices_[0], device_buffer.ptr, host_ptr, bytes, 1), "CopyToDevice");
 }
 void BackendB200::CopyToHost(const DeviceBuffer& device_buffer, void* host_ptr, size_t bytes) {
     if (bytes > device_buffer.size) throw std::invalid_argument("BackendB200::CopyToHost: buffer too small");
-    check(luxb200_dev_copy(device_, host_ptr, device_buffer.ptr, bytes, 2), "CopyToHost");
+    check(luxb200_dev_copy(devices_[0], host_ptr, device_buffer.ptr, bytes, 2), "CopyToHost");
 }
 void BackendB200::Synchronize() {
-    if (h_) check(luxb200_synchronize(h_), "Synchronize");
+    for (luxb200_ctx* h : hs_) check(luxb200_synchronize(h), "Synchronize");
 }
 
 // ---- blind rotation: RingGSWAccumulator::EvalAcc (rgsw-acc.h:73-76) on EVALUATION-format accumulators -----
@@ -311,7 +435,8 @@ void BackendB200::LoadPacked(const uint8_t* bsk, size_t bsk_size, const uint8_t*
         }
         if (pos != flat.size()) throw std::invalid_argument("BackendB200::LoadPacked: packed bootstrapping key is incomplete");
         check(luxb200_load_bsk(h_, flat.data(), 0), "load_bsk");
-        bound_bsk_ = bsk;
+        bound_bsk_.reset();
+        packed_bsk_ = true;
     }
     if (ksk) {
         PackedKSKView v;
@@ -322,8 +447,10 @@ void BackendB200::LoadPacked(const uint8_t* bsk, size_t bsk_size, const uint8_t*
         for (size_t t = 0; t < A.size(); ++t) A[t] = v.coeff(v.A, t);
         for (size_t t = 0; t < B.size(); ++t) B[t] = v.coeff(v.B, t);
         check(luxb200_load_ksk(h_, A.data(), B.data(), 0), "load_ksk");
-        bound_ksk_ = ksk;
+        bound_ksk_.reset();
+        packed_ksk_ = true;
     }
+    share_keys();
 }
 
 DeviceBuffer BackendB200::PackBootstrappingKey(const RingGSWACCKey& ek) {
@@ -408,66 +535,147 @@ void BackendB200::UnpackCiphertexts(const DeviceBuffer& packed, std::vector<LWEC
 }
 
 // ---- gate-level entry points (BinFHEScheme::EvalBinGate / Bootstrap / EvalFunc, binfhe-base-scheme.cpp:76-332) --
+// One homogeneous group of 2-input gates: every ct1 has plaintext modulus p and one format, every ct2 one format.
+void BackendB200::gate2(BINGATE gate, const std::vector<LWECiphertext>& ct1, const std::vector<LWECiphertext>& ct2,
+                        std::vector<LWECiphertext>& out) {
+    const size_t cnt = ct1.size();
+    const uint32_t n = p_.n, N = p_.N;
+    const bool e1 = u64(ct1[0]->GetModulus()) == p_.Q, e2 = u64(ct2[0]->GetModulus()) == p_.Q;   // binfhe-base-scheme.cpp:92-93
+    const uint32_t l1 = e1 ? N : n, l2 = e2 ? N : n;
+    const uint64_t pm = u64(ct1[0]->GetptModulus());
+    const double t0 = now_ms();
+    uint64_t *a1 = st_[0].ensure(cnt * size_t(l1)), *b1 = st_[1].ensure(cnt), *a2 = st_[2].ensure(cnt * size_t(l2)),
+             *b2 = st_[3].ensure(cnt), *oa = st_[4].ensure(cnt * size_t(n)), *ob = st_[5].ensure(cnt);
+    flatten_cts_to(ct1.data(), cnt, l1, e1 ? p_.Q : p_.q, a1, b1);
+    flatten_cts_to(ct2.data(), cnt, l2, e2 ? p_.Q : p_.q, a2, b2);
+    const double t1 = now_ms();
+    const int in_ext = (e1 ? 1 : 0) | (e2 ? 2 : 0);
+    run_split(cnt, [&](size_t d, size_t lo, size_t hi) {
+        const int rc = luxb200_evalbingate_batch_ex(hs_[d], static_cast<int>(gate), a1 + lo * l1, b1 + lo, a2 + lo * l2, b2 + lo,
+                                                    oa + lo * n, ob + lo, hi - lo, 0, pm, in_ext);
+        if (rc != LUXB200_OK) throw std::runtime_error(std::string("BackendB200::EvalBinGate: ") + luxb200_last_error());
+    });
+    const double t2 = now_ms();
+    out.resize(cnt);
+    build_cts_from(oa, ob, cnt, n, NativeInteger(p_.q), NativeInteger(4), out.data());   // a fresh ciphertext: m_p = 4
+    timing_ = Timing{t1 - t0, t2 - t1, now_ms() - t2};
+}
+
 void BackendB200::EvalBinGate(BINGATE gate, const std::vector<LWECiphertext>& ct1, const std::vector<LWECiphertext>& ct2,
                               std::vector<LWECiphertext>& out) {
     if (ct1.size() != ct2.size()) throw std::invalid_argument("Input size mismatch");
     if (ct1.empty()) { out.clear(); return; }
-    std::vector<uint64_t> a1, b1, a2, b2, oa(ct1.size() * size_t(p_.n)), ob(ct1.size());
-    flatten_cts(ct1, p_.n, a1, b1);
-    flatten_cts(ct2, p_.n, a2, b2);
-    check(luxb200_evalbingate_batch(h_, static_cast<int>(gate), a1.data(), b1.data(), a2.data(), b2.data(), oa.data(),
-                                    ob.data(), ct1.size(), 0), "EvalBinGate");
-    build_cts(oa, ob, p_.n, NativeInteger(p_.q), NativeInteger(4), out);
+    std::lock_guard<std::recursive_mutex> lk(mu_);
+    // per-element checks of BinFHEScheme::EvalBinGate (binfhe-base-scheme.cpp:81-86) and the properties one device call
+    // shares across its batch: plaintext modulus of ct1 and the SMALL_DIM / extended format of either operand
+    bool uniform = true;
+    for (size_t i = 0; i < ct1.size(); ++i) {
+        if (!ct1[i]) throw std::invalid_argument("Ciphertext1 is empty");
+        if (!ct2[i]) throw std::invalid_argument("Ciphertext2 is empty");
+        if (ct1[i] == ct2[i]) throw std::invalid_argument("Input ciphertexts should be independant");
+        uniform = uniform && ct1[i]->GetptModulus() == ct1[0]->GetptModulus() && ct1[i]->GetModulus() == ct1[0]->GetModulus() &&
+                  ct2[i]->GetModulus() == ct2[0]->GetModulus();
+    }
+    if (uniform) { gate2(gate, ct1, ct2, out); return; }
+    // mixed batch: one device call per (p, format of ct1, format of ct2) group, results scattered back in order
+    std::map<std::tuple<uint64_t, uint64_t, uint64_t>, std::vector<size_t>> groups;
+    for (size_t i = 0; i < ct1.size(); ++i)
+        groups[{u64(ct1[i]->GetptModulus()), u64(ct1[i]->GetModulus()), u64(ct2[i]->GetModulus())}].push_back(i);
+    out.assign(ct1.size(), nullptr);
+    for (const auto& g : groups) {
+        std::vector<LWECiphertext> x, y, r;
+        for (size_t i : g.second) { x.push_back(ct1[i]); y.push_back(ct2[i]); }
+        gate2(gate, x, y, r);
+        for (size_t k = 0; k < g.second.size(); ++k) out[g.second[k]] = r[k];
+    }
 }
+
 void BackendB200::EvalBinGateMulti(BINGATE gate, const std::vector<std::vector<LWECiphertext>>& cts,
                                    std::vector<LWECiphertext>& out) {
     if (cts.empty()) { out.clear(); return; }
+    std::lock_guard<std::recursive_mutex> lk(mu_);
     const uint32_t k = static_cast<uint32_t>(cts[0].size()), n = p_.n;
+    if (k == 0) throw std::invalid_argument("Input size mismatch");
+    const NativeInteger pm = cts[0][0]->GetptModulus();
     std::vector<uint64_t> a(cts.size() * size_t(k) * n), b(cts.size() * size_t(k)), oa(cts.size() * size_t(n)), ob(cts.size());
     for (size_t i = 0; i < cts.size(); ++i) {
         if (cts[i].size() != k) throw std::invalid_argument("Input size mismatch");
-        std::vector<uint64_t> ai, bi;
-        flatten_cts(cts[i], n, ai, bi);
-        std::memcpy(&a[i * k * n], ai.data(), ai.size() * 8);
-        std::memcpy(&b[i * k], bi.data(), bi.size() * 8);
+        for (uint32_t x = 0; x < k; ++x)
+            for (uint32_t y = x + 1; y < k; ++y)
+                if (cts[i][x] == cts[i][y]) throw std::invalid_argument("Input ciphertexts should be independent");
+        if (!cts[i][0] || cts[i][0]->GetptModulus() != pm)
+            throw std::invalid_argument("BackendB200::EvalBinGateMulti: one batch = one plaintext modulus (split the batch)");
+        // inputs mod q; an extended input (N, Q) is not accepted here: switch it down first (KeySwitchBatch + ModSwitchBatch)
+        flatten_cts_to(cts[i].data(), k, n, p_.q, &a[i * k * n], &b[i * k]);
     }
-    check(luxb200_evalbingate_multi_batch(h_, static_cast<int>(gate), k, a.data(), b.data(), oa.data(), ob.data(), cts.size(),
-                                          u64(cts[0][0]->GetptModulus())), "EvalBinGateMulti");
-    build_cts(oa, ob, n, NativeInteger(p_.q), cts[0][0]->GetptModulus(), out);
+    run_split(cts.size(), [&](size_t d, size_t lo, size_t hi) {
+        const int rc = luxb200_evalbingate_multi_batch(hs_[d], static_cast<int>(gate), k, &a[lo * k * n], &b[lo * k], &oa[lo * n],
+                                                       &ob[lo], hi - lo, u64(pm));
+        if (rc != LUXB200_OK) throw std::runtime_error(std::string("BackendB200::EvalBinGateMulti: ") + luxb200_last_error());
+    });
+    // CMUX ends in a 2-input NAND (a fresh ciphertext, m_p = 4); the sum gates SetptModulus(p) (binfhe-base-scheme.cpp:171)
+    build_cts(oa, ob, n, NativeInteger(p_.q), gate == CMUX ? NativeInteger(4) : pm, out);
 }
+
 void BackendB200::Bootstrap(const std::vector<LWECiphertext>& in, std::vector<LWECiphertext>& out) {
     if (in.empty()) { out.clear(); return; }
-    std::vector<uint64_t> a, b, oa(in.size() * size_t(p_.n)), ob(in.size());
-    flatten_cts(in, p_.n, a, b);
-    check(luxb200_bootstrap_batch(h_, a.data(), b.data(), oa.data(), ob.data(), in.size(), u64(in[0]->GetptModulus()), 0),
-          "Bootstrap");
-    build_cts(oa, ob, p_.n, NativeInteger(p_.q), in[0]->GetptModulus(), out);
+    std::lock_guard<std::recursive_mutex> lk(mu_);
+    const uint32_t n = p_.n;
+    for (const auto& ct : in) {
+        if (!ct) throw std::invalid_argument("Ciphertext is empty");
+        if (ct->GetptModulus() != in[0]->GetptModulus())
+            throw std::invalid_argument("BackendB200::Bootstrap: one batch = one plaintext modulus (split the batch)");
+    }
+    uint64_t *a = st_[0].ensure(in.size() * size_t(n)), *b = st_[1].ensure(in.size()), *oa = st_[4].ensure(in.size() * size_t(n)),
+             *ob = st_[5].ensure(in.size());
+    flatten_cts_to(in.data(), in.size(), n, p_.q, a, b);
+    const uint64_t pm = u64(in[0]->GetptModulus());
+    run_split(in.size(), [&](size_t d, size_t lo, size_t hi) {
+        const int rc = luxb200_bootstrap_batch(hs_[d], a + lo * n, b + lo, oa + lo * n, ob + lo, hi - lo, pm, 0);
+        if (rc != LUXB200_OK) throw std::runtime_error(std::string("BackendB200::Bootstrap: ") + luxb200_last_error());
+    });
+    out.resize(in.size());
+    build_cts_from(oa, ob, in.size(), n, NativeInteger(p_.q), in[0]->GetptModulus(), out.data());
 }
+
 void BackendB200::EvalCircuit(const std::vector<LWECiphertext>& inputs, const std::vector<luxb200_gate>& gates,
                               const std::vector<uint32_t>& outputs, std::vector<LWECiphertext>& out) {
     if (outputs.empty()) { out.clear(); return; }
-    std::vector<uint64_t> a, b, oa(outputs.size() * size_t(p_.n)), ob(outputs.size());
-    flatten_cts(inputs, p_.n, a, b);   // [n_inputs][count = 1][n]
+    std::lock_guard<std::recursive_mutex> lk(mu_);
+    std::vector<uint64_t> a(inputs.size() * size_t(p_.n)), b(inputs.size()), oa(outputs.size() * size_t(p_.n)), ob(outputs.size());
+    flatten_cts_to(inputs.data(), inputs.size(), p_.n, p_.q, a.data(), b.data());   // [n_inputs][count = 1][n]
     check(luxb200_circuit_batch(h_, static_cast<uint32_t>(inputs.size()), gates.data(), static_cast<uint32_t>(gates.size()),
                                 outputs.data(), static_cast<uint32_t>(outputs.size()), a.data(), b.data(), oa.data(), ob.data(),
                                 1), "EvalCircuit");
     build_cts(oa, ob, p_.n, NativeInteger(p_.q), NativeInteger(4), out);
 }
+
 void BackendB200::EvalFunc(const std::vector<LWECiphertext>& in, const std::vector<NativeInteger>& lut, const NativeInteger& beta,
                            std::vector<LWECiphertext>& out) {
     if (in.empty()) { out.clear(); return; }
-    std::vector<uint64_t> a, b, l(lut.size()), oa(in.size() * size_t(p_.n)), ob(in.size());
-    flatten_cts(in, p_.n, a, b);
-    for (size_t i = 0; i < lut.size(); ++i) l[i] = u64(lut[i]);
+    std::lock_guard<std::recursive_mutex> lk(mu_);
+    const uint32_t n = p_.n;
+    if (!in[0]) throw std::invalid_argument("Ciphertext is empty");
     const uint64_t ctmod = u64(in[0]->GetModulus());
-    check(luxb200_evalfunc_batch(h_, a.data(), b.data(), l.data(), l.size(), u64(beta), oa.data(), ob.data(), in.size(), ctmod),
-          "EvalFunc");
-    build_cts(oa, ob, p_.n, NativeInteger(ctmod), in[0]->GetptModulus(), out);
+    std::vector<uint64_t> l(lut.size());
+    for (size_t i = 0; i < lut.size(); ++i) l[i] = u64(lut[i]);
+    uint64_t *a = st_[0].ensure(in.size() * size_t(n)), *b = st_[1].ensure(in.size()), *oa = st_[4].ensure(in.size() * size_t(n)),
+             *ob = st_[5].ensure(in.size());
+    flatten_cts_to(in.data(), in.size(), n, ctmod, a, b);   // every element: dimension n and the modulus of the LUT
+    run_split(in.size(), [&](size_t d, size_t lo, size_t hi) {
+        const int rc = luxb200_evalfunc_batch(hs_[d], a + lo * n, b + lo, l.data(), l.size(), u64(beta), oa + lo * n, ob + lo,
+                                              hi - lo, ctmod);
+        if (rc != LUXB200_OK) throw std::runtime_error(std::string("BackendB200::EvalFunc: ") + luxb200_last_error());
+    });
+    out.resize(in.size());
+    build_cts_from(oa, ob, in.size(), n, NativeInteger(ctmod), NativeInteger(4), out.data());   // fresh ciphertexts: m_p = 4
 }
 
-BackendB200* RegisterB200(BinFHEContext& cc, int device) {
-    auto be = std::make_unique<BackendB200>(device);
-    if (!be->IsAvailable()) throw std::runtime_error("RegisterB200: no CUDA device " + std::to_string(device) + " (there is no CPU fallback)");
+BackendB200* RegisterB200(BinFHEContext& cc, const std::vector<int>& devices) {
+    auto be = std::make_unique<BackendB200>(devices);
+    if (!be->IsAvailable())
+        throw std::runtime_error("RegisterB200: CUDA device " + std::to_string(be->device()) +
+                                 " (or another requested one) is not present (there is no CPU fallback)");
     be->Bind(cc);
     BackendB200* raw = be.get();
     auto& reg = BackendRegistry::Instance();
@@ -475,6 +683,7 @@ BackendB200* RegisterB200(BinFHEContext& cc, int device) {
     reg.SetDefault(BackendType::CUDA);
     return raw;
 }
+BackendB200* RegisterB200(BinFHEContext& cc, int device) { return RegisterB200(cc, std::vector<int>{device}); }
 
 }  // namespace backend
 }  // namespace lux::fhe

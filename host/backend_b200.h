@@ -9,7 +9,9 @@
 #pragma once
 #include <luxb200.h>
 
+#include <functional>
 #include <memory>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -22,14 +24,24 @@ namespace backend {
 class BackendB200 final : public Backend {
 public:
     explicit BackendB200(int device = 0);
+    // Several GPUs of one box behind one backend: one device context (stream, work buffers) per GPU, the keys uploaded once
+    // to devices[0] and copied peer-to-peer over NVLink (luxb200_broadcast_keys), every batch split into contiguous
+    // count/G slices that run concurrently, one host thread per GPU.  No collective on the per-gate path.
+    explicit BackendB200(std::vector<int> devices);
     ~BackendB200() override;
 
-    // Create the device context for cc's parameters and upload cc's refresh and switching keys (after BTKeyGen).
+    // Create the device context(s) for cc's parameters and upload cc's refresh and switching keys (after BTKeyGen).
     // Throws lux::fhe::config_error-style std::runtime_error on failure; there is no CPU fallback.
     void Bind(BinFHEContext& cc);
+    // Make the resident parameters and keys those of `cc`: rebinds when cc's parameter set differs from the bound one and
+    // reloads whichever of cc's current refresh / switching key objects is not the resident one (a second BTKeyGen, or a
+    // second BinFHEContext in the process).  The batch API calls this on every entry, so a batch never runs on stale or
+    // foreign keys.  A context without keys keeps keys loaded with LoadPacked.
+    void Attach(BinFHEContext& cc);
     bool IsBound() const { return h_ != nullptr; }
     luxb200_ctx* handle() const { return h_; }
-    int device() const { return device_; }
+    int device() const { return devices_[0]; }
+    size_t NumDevices() const { return devices_.size(); }
 
     BackendType Type() const override { return BackendType::CUDA; }
     std::string Name() const override { return "B200 (libluxb200, sm_100a)"; }
@@ -82,25 +94,52 @@ public:
     void EvalCircuit(const std::vector<LWECiphertext>& inputs, const std::vector<luxb200_gate>& gates,
                      const std::vector<uint32_t>& outputs, std::vector<LWECiphertext>& out);
 
+    // host time (ms) the last gate-level call spent packing inputs / building outputs, and inside the C ABI call
+    struct Timing { double pack_ms = 0, call_ms = 0, unpack_ms = 0; };
+    Timing LastTiming() const { return timing_; }
+
 private:
+    // grow-only page-locked staging buffer (luxb200_host_alloc)
+    struct Pinned {
+        uint64_t* p = nullptr;
+        size_t cap = 0;
+        uint64_t* ensure(size_t elems);
+        void release();
+    };
     void check(int rc, const char* what) const;
     void flatten_bsk(const RingGSWACCKeyImpl& ek, std::vector<uint64_t>& out) const;
     void load_keys(const RingGSWACCKey& ek, const LWESwitchingKey& ks);
     void ensure_bsk(const RingGSWACCKey& ek);
     void ensure_ksk(const LWESwitchingKey& ks);
+    void share_keys();
+    void destroy_contexts();
+    // contiguous [lo, hi) slices of a batch over the devices (sizes differ by at most one); body(device index, lo, hi) runs
+    // on one host thread per device; the first exception is rethrown
+    void run_split(size_t count, const std::function<void(size_t, size_t, size_t)>& body);
+    void gate2(BINGATE gate, const std::vector<LWECiphertext>& ct1, const std::vector<LWECiphertext>& ct2,
+               std::vector<LWECiphertext>& out);
 
-    int device_;
+    std::vector<int> devices_;
+    std::vector<luxb200_ctx*> hs_;      // one context per device; h_ == hs_[0]
     luxb200_ctx* h_ = nullptr;
     luxb200_params p_{};
     uint32_t digitsG_ = 0, digitsR_ = 0, rows_ = 0;
     std::shared_ptr<ILNativeParams> poly_params_;
-    const void* bound_bsk_ = nullptr;   // identity of the key objects currently resident on the device
-    const void* bound_ksk_ = nullptr;
+    // the key OBJECTS resident on the device(s), held so that their addresses cannot be recycled by a new key while they
+    // serve as the cache identity; packed_* for keys that came from LoadPacked bytes
+    RingGSWACCKey bound_bsk_;
+    LWESwitchingKey bound_ksk_;
+    bool packed_bsk_ = false, packed_ksk_ = false;
+    std::recursive_mutex mu_;           // entry points serialise: staging buffers and key binding are shared state
+    Pinned st_[6];
+    Timing timing_;
 };
 
 // Registers a BackendB200 bound to cc with the reference's registry and makes it the default backend.
 // Returns the registered instance (owned by the registry).
 BackendB200* RegisterB200(BinFHEContext& cc, int device = 0);
+// The same over several GPUs of the box (devices = {0, 1, ...}); an empty list means every visible GPU.
+BackendB200* RegisterB200(BinFHEContext& cc, const std::vector<int>& devices);
 
 }  // namespace backend
 }  // namespace lux::fhe

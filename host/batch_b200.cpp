@@ -21,10 +21,14 @@ namespace lux::fhe {
 
 namespace {
 
-backend::BackendB200* b200() {
+// The registered B200 backend, attached to `cc`: its resident parameters and keys are made cc's (BackendB200::Attach), so
+// a second BTKeyGen or a second BinFHEContext in the process never runs on stale or foreign keys — the reference always
+// uses cc's current keys (binfhecontext.cpp:310-322).
+backend::BackendB200* b200(BinFHEContext& cc) {
     auto* be = dynamic_cast<backend::BackendB200*>(backend::BackendRegistry::Instance().Get(backend::BackendType::CUDA));
     if (!be || !be->IsBound())
         throw std::runtime_error("B200 backend is not registered (call backend::RegisterB200 after BTKeyGen); no CPU fallback");
+    be->Attach(cc);
     return be;
 }
 
@@ -54,7 +58,7 @@ BatchResult BootstrapBatch(BinFHEContext& cc, const std::vector<LWECiphertext>& 
             ct_out.resize(ct_in.size());
             for (size_t i = 0; i < ct_in.size(); ++i) ct_out[i] = cc.Bootstrap(ct_in[i]);
         } else {
-            b200()->Bootstrap(ct_in, ct_out);
+            b200(cc)->Bootstrap(ct_in, ct_out);
         }
     });
 }
@@ -66,7 +70,7 @@ BatchResult EvalFuncBatch(BinFHEContext& cc, const std::vector<LWECiphertext>& c
             ct_out.resize(ct_in.size());
             for (size_t i = 0; i < ct_in.size(); ++i) ct_out[i] = cc.EvalFunc(ct_in[i], lut);
         } else {
-            b200()->EvalFunc(ct_in, lut, cc.GetBeta(), ct_out);
+            b200(cc)->EvalFunc(ct_in, lut, cc.GetBeta(), ct_out);
         }
     });
 }
@@ -85,7 +89,7 @@ BatchResult EvalFuncMultiOutputBatch(BinFHEContext& cc, const std::vector<LWECip
                 col.resize(ct_in.size());
                 for (size_t i = 0; i < ct_in.size(); ++i) col[i] = cc.EvalFunc(ct_in[i], luts[j]);
             } else {
-                b200()->EvalFunc(ct_in, luts[j], cc.GetBeta(), col);
+                b200(cc)->EvalFunc(ct_in, luts[j], cc.GetBeta(), col);
             }
             for (size_t i = 0; i < ct_in.size(); ++i) ct_out[i * m + j] = col[i];
         }
@@ -100,7 +104,7 @@ BatchResult EvalBinGateBatch(BinFHEContext& cc, BINGATE gate, const std::vector<
             ct_out.resize(ct1.size());
             for (size_t i = 0; i < ct1.size(); ++i) ct_out[i] = cc.EvalBinGate(gate, ct1[i], ct2[i]);
         } else {
-            b200()->EvalBinGate(gate, ct1, ct2, ct_out);
+            b200(cc)->EvalBinGate(gate, ct1, ct2, ct_out);
         }
     });
 }
@@ -119,7 +123,7 @@ BatchResult EvalCMUXBatch(BinFHEContext& cc, const std::vector<LWECiphertext>& c
         } else {
             std::vector<std::vector<LWECiphertext>> in(ct_sel.size());
             for (size_t i = 0; i < ct_sel.size(); ++i) in[i] = {ct_sel[i], ct_true[i], ct_false[i]};
-            b200()->EvalBinGateMulti(CMUX, in, ct_out);
+            b200(cc)->EvalBinGateMulti(CMUX, in, ct_out);
         }
     });
 }
@@ -127,13 +131,13 @@ BatchResult EvalCMUXBatch(BinFHEContext& cc, const std::vector<LWECiphertext>& c
 BatchResult KeySwitchBatch(BinFHEContext& cc, const std::vector<LWECiphertext>& ct_in, std::vector<LWECiphertext>& ct_out,
                            uint32_t) {
     return guarded(ct_in.size(), [&] {
-        b200()->KeySwitchBatch(cc.GetParams()->GetLWEParams(), ct_in, cc.GetSwitchKey(), ct_out);
+        b200(cc)->KeySwitchBatch(cc.GetParams()->GetLWEParams(), ct_in, cc.GetSwitchKey(), ct_out);
     });
 }
 
 BatchResult ModSwitchBatch(BinFHEContext& cc, const std::vector<LWECiphertext>& ct_in, std::vector<LWECiphertext>& ct_out,
                            uint32_t) {
-    return guarded(ct_in.size(), [&] { b200()->ModSwitchBatch(cc.GetParams()->GetLWEParams(), ct_in, ct_out); });
+    return guarded(ct_in.size(), [&] { b200(cc)->ModSwitchBatch(cc.GetParams()->GetLWEParams(), ct_in, ct_out); });
 }
 
 // ---- async variants (binfhe-batch.h:181-223): one std::async thread per call, like batch.cpp:320-349 ------------
@@ -249,7 +253,7 @@ static bool execute_on_device(BinFHEContext& cc, std::vector<LWECiphertext>& cts
         outs.push_back(w);
     }
     std::vector<LWECiphertext> res;
-    b200()->EvalCircuit(inputs, gates, outs, res);
+    b200(cc)->EvalCircuit(inputs, gates, outs, res);
     for (size_t i = 0; i < ops.size(); ++i) cts[ops[i].output_ids[0]] = res[i];
     result.processed = ops.size();
     return true;

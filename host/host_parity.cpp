@@ -2,14 +2,23 @@
 // keys and ciphertexts; the batch API (host/batch_b200.cpp) and the backend seam (host/backend_b200.cpp) run on the
 // B200; every output is compared coefficient by coefficient with what the reference's CPU code returns for the same
 // inputs (cc.EvalBinGate / Bootstrap / EvalFunc / EvalAcc / KeySwitch / ModSwitch).  TEST INFRASTRUCTURE: links the
-// reference library built by oracle/Makefile.  usage: host_parity <TOY|STD128|STD128_AP|STD128_LMKCDEY> [count] [pairs]
+// reference library built by oracle/Makefile.
+// usage: host_parity <TOY|STD128|STD128_AP|STD128_LMKCDEY|...> [count] [pairs] [--devices G] [--e2e GATES] [--dcrt]
+//   --devices G  one BackendB200 over GPUs 0..G-1 (keys copied peer-to-peer, every batch split over the devices)
+//   --e2e GATES  also time lux::fhe::EvalBinGateBatch(cc, AND, ...) on GATES LWECiphertext pairs (the call a reference user
+//                makes: reference containers in, reference containers out) and print e2e_cpp
+//   --dcrt       also check host/dcrt_b200 against DCRTPoly::SwitchFormat at N = 2^16, 32 limbs of 60 bits
 #include <cstdio>
 #include <cstdlib>
 #include <functional>
 #include <random>
 #include <string>
 
+#include <chrono>
+#include <cstring>
+
 #include "backend_b200.h"
+#include "dcrt_b200.h"
 #include "batch/binfhe-batch.h"
 #include "rgsw-acc-cggi.h"
 #include "rgsw-acc-dm.h"
@@ -71,10 +80,60 @@ static int greater_than8_plain(unsigned a, unsigned b) {   // the same circuit o
     return r;
 }
 
+static double wall_ms() {
+    return std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now().time_since_epoch()).count();
+}
+
+// DCRTPolyImpl::SwitchFormat (dcrtpoly-impl.h:1953-1959) on the CPU vs host/dcrt_b200 (one luxb200_ntt_batch call), every limb
+static void dcrt_check(uint32_t N, uint32_t L, uint32_t bits, size_t count) {
+    auto params = std::make_shared<ILDCRTParams<BigInteger>>(2 * N, L, bits);
+    std::mt19937_64 rng(99);
+    std::vector<DCRTPoly> gpu, cpu;
+    for (size_t i = 0; i < count; ++i) {
+        DCRTPoly p(params, Format::COEFFICIENT, true);
+        for (uint32_t l = 0; l < L; ++l) {
+            NativePoly& limb = p.GetAllElements()[l];
+            const uint64_t q = limb.GetModulus().ConvertToInt<uint64_t>();
+            for (uint32_t k = 0; k < N; ++k) limb[k] = NativeInteger(rng() % q);
+            if (i == 0 && l == 0) for (uint32_t k = 0; k < N; ++k) limb[k] = NativeInteger(q - 1);
+        }
+        gpu.push_back(p);
+        cpu.push_back(std::move(p));
+    }
+    backend::DCRTNttB200 ntt(0);
+    std::vector<DCRTPoly*> ptrs;
+    for (auto& p : gpu) ptrs.push_back(&p);
+    const double t0 = wall_ms();
+    ntt.SwitchFormat(ptrs);
+    const double t1 = wall_ms();
+    for (auto& p : cpu) p.SwitchFormat();
+    const double t2 = wall_ms();
+    size_t bad = 0;
+    for (size_t i = 0; i < count; ++i) bad += !(gpu[i] == cpu[i]) || gpu[i].GetFormat() != Format::EVALUATION;
+    report("DCRT_SwitchFormat_forward", count * L, bad);
+    ntt.SwitchFormat(ptrs);
+    for (auto& p : cpu) p.SwitchFormat();
+    bad = 0;
+    for (size_t i = 0; i < count; ++i) bad += !(gpu[i] == cpu[i]) || gpu[i].GetFormat() != Format::COEFFICIENT;
+    report("DCRT_SwitchFormat_inverse", count * L, bad);
+    std::printf("DCRT N=%u L=%u x%zu: B200 seam %.1f ms (host packing + PCIe included), reference CPU %.1f ms\n", N, L, count, t1 - t0,
+                t2 - t1);
+}
+
 int main(int argc, char** argv) {
-    const std::string set = argc > 1 ? argv[1] : "STD128";
-    const size_t cnt = argc > 2 ? std::strtoul(argv[2], nullptr, 10) : 8;
-    const size_t pairs = argc > 3 ? std::strtoul(argv[3], nullptr, 10) : 2;
+    std::vector<std::string> pos;
+    size_t n_dev = 1, e2e_gates = 0;
+    bool dcrt = false;
+    for (int i = 1; i < argc; ++i) {
+        const std::string a = argv[i];
+        if (a == "--devices" && i + 1 < argc) n_dev = std::strtoul(argv[++i], nullptr, 10);
+        else if (a == "--e2e" && i + 1 < argc) e2e_gates = std::strtoul(argv[++i], nullptr, 10);
+        else if (a == "--dcrt") dcrt = true;
+        else pos.push_back(a);
+    }
+    const std::string set = pos.size() > 0 ? pos[0] : "STD128";
+    const size_t cnt = pos.size() > 1 ? std::strtoul(pos[1].c_str(), nullptr, 10) : 8;
+    const size_t pairs = pos.size() > 2 ? std::strtoul(pos[2].c_str(), nullptr, 10) : 2;
     BINFHE_PARAMSET ps = STD128;
     BINFHE_METHOD method = GINX;
     if (set == "TOY") ps = TOY;
@@ -91,9 +150,11 @@ int main(int argc, char** argv) {
     cc.GenerateBinFHEContext(ps, method);
     auto sk = cc.KeyGen();
     cc.BTKeyGen(sk);
-    auto* be = backend::RegisterB200(cc, 0);
-    std::printf("backend: %s, device memory %.1f GB, default=%s\n", be->Name().c_str(), be->DeviceMemory() / 1e9,
-                backend::BackendTypeName(backend::CurrentBackend()->Type()).c_str());
+    std::vector<int> devs;
+    for (size_t d = 0; d < n_dev; ++d) devs.push_back(static_cast<int>(d));
+    auto* be = backend::RegisterB200(cc, devs);
+    std::printf("backend: %s, %zu device(s), device memory %.1f GB, default=%s\n", be->Name().c_str(), be->NumDevices(),
+                be->DeviceMemory() / 1e9, backend::BackendTypeName(backend::CurrentBackend()->Type()).c_str());
 
     std::mt19937 rng(12345);
     std::vector<int> m1(cnt), m2(cnt), m3(cnt);
@@ -346,6 +407,113 @@ int main(int argc, char** argv) {
         be->Free(cb);
         report("Backend_PackUnpackCiphertexts", cnt, count_diff(rt, c1));
     }
-    std::printf("{\"host_parity\": \"%s\", \"failed_checks\": %d, %s}\n", set.c_str(), g_fail, g_json.c_str());
+    // ---- reference edge cases at the seam (binfhe-base-scheme.cpp:81-93) -------------------------------------------
+    {
+        // (a) "extended" inputs — dimension N, modulus Q — are switched down first (SwitchCTtoqn), per operand
+        const size_t m = std::min<size_t>(cnt, 6);
+        std::vector<LWECiphertext> x(m), y(c2.begin(), c2.begin() + m), gpu, cpu(m);
+#pragma omp parallel for
+        for (size_t i = 0; i < m; ++i) x[i] = cc.EvalBinGate(OR, c1[i], c3[i], true);   // extended result of the reference
+        auto r = EvalBinGateBatch(cc, NAND, x, y, gpu);
+        size_t bad = r.success ? 0 : m;
+        if (!r.success) std::printf("extended ct1: %s\n", r.error.c_str());
+#pragma omp parallel for
+        for (size_t i = 0; i < m; ++i) cpu[i] = cc.EvalBinGate(NAND, x[i], y[i]);
+        if (r.success) bad += count_diff(gpu, cpu);
+        r = EvalBinGateBatch(cc, XOR, y, x, gpu);                                      // extended ct2
+#pragma omp parallel for
+        for (size_t i = 0; i < m; ++i) cpu[i] = cc.EvalBinGate(XOR, y[i], x[i]);
+        bad += r.success ? count_diff(gpu, cpu) : m;
+        // mixed batch: extended and SMALL_DIM ct1 in one call
+        std::vector<LWECiphertext> mix(m);
+        for (size_t i = 0; i < m; ++i) mix[i] = (i & 1) ? x[i] : c1[i];
+        r = EvalBinGateBatch(cc, AND, mix, y, gpu);
+#pragma omp parallel for
+        for (size_t i = 0; i < m; ++i) cpu[i] = cc.EvalBinGate(AND, mix[i], y[i]);
+        bad += r.success ? count_diff(gpu, cpu) : m;
+        report("EvalBinGateBatch_extended_inputs", 3 * m, bad);
+        // (b) the same ciphertext object on both sides is refused with the reference's message
+        std::vector<LWECiphertext> o;
+        r = EvalBinGateBatch(cc, AND, c1, c1, o);
+        report("EvalBinGateBatch_same_ct_refused", 1, (!r.success && r.error.find("independant") != std::string::npos) ? 0 : 1);
+        // (c) the plaintext modulus of ct1 reaches the test vector (BootstrapGateCore, :535-567)
+        std::vector<LWECiphertext> p8(m);
+        for (size_t i = 0; i < m; ++i) { p8[i] = std::make_shared<LWECiphertextImpl>(*c1[i]); p8[i]->SetptModulus(NativeInteger(8)); }
+        r = EvalBinGateBatch(cc, OR, p8, y, gpu);
+#pragma omp parallel for
+        for (size_t i = 0; i < m; ++i) cpu[i] = cc.EvalBinGate(OR, p8[i], y[i]);
+        report("EvalBinGateBatch_ptmodulus", m, r.success ? count_diff(gpu, cpu) : m);
+    }
+    // ---- two async futures in flight on one backend (batch.cpp:320-349 runs them on std::async threads) -----------
+    {
+        std::vector<LWECiphertext> g1, g2, cpu1(cnt), cpu2(cnt);
+        auto f1 = BootstrapBatchAsync(cc, c1, g1);
+        auto f2 = BootstrapBatchAsync(cc, c2, g2);
+        auto r1 = f1.Wait(), r2 = f2.Wait();
+#pragma omp parallel for
+        for (size_t i = 0; i < cnt; ++i) { cpu1[i] = cc.Bootstrap(c1[i]); cpu2[i] = cc.Bootstrap(c2[i]); }
+        report("Async_overlapping_futures", 2 * cnt, (r1.success && r2.success) ? count_diff(g1, cpu1) + count_diff(g2, cpu2) : 2 * cnt);
+    }
+    // ---- e2e through the reference's own call: EvalBinGateBatch(cc, AND, vector<LWECiphertext> ...) -----------------
+    if (e2e_gates) {
+        std::vector<LWECiphertext> x(e2e_gates), y(e2e_gates), o;
+        std::vector<int> mx(e2e_gates), my(e2e_gates);
+#pragma omp parallel for
+        for (size_t i = 0; i < e2e_gates; ++i) {
+            mx[i] = (i * 7 + 1) & 1; my[i] = (i * 13 + 5) >> 2 & 1;
+            x[i] = cc.Encrypt(sk, mx[i]); y[i] = cc.Encrypt(sk, my[i]);
+        }
+        EvalBinGateBatch(cc, AND, x, y, o);   // warm-up (staging buffers, kernels)
+        double best = 1e30;
+        backend::BackendB200::Timing tm;
+        for (int rep = 0; rep < 3; ++rep) {
+            o.clear();
+            const double t0 = wall_ms();
+            auto r = EvalBinGateBatch(cc, AND, x, y, o);
+            const double dt = wall_ms() - t0;
+            if (!r.success) { std::printf("e2e EvalBinGateBatch failed: %s\n", r.error.c_str()); return 2; }
+            if (dt < best) { best = dt; tm = be->LastTiming(); }
+        }
+        size_t bad = 0;
+        for (size_t i = 0; i < e2e_gates; ++i) { LWEPlaintext d; cc.Decrypt(sk, o[i], &d); bad += d != (mx[i] & my[i]); }
+        std::vector<LWECiphertext> cpu(std::min<size_t>(e2e_gates, 64));
+#pragma omp parallel for
+        for (size_t i = 0; i < cpu.size(); ++i) cpu[i] = cc.EvalBinGate(AND, x[i], y[i]);
+        for (size_t i = 0; i < cpu.size(); ++i) bad += !same_ct(o[i], cpu[i]);
+        report("e2e_cpp_correct", e2e_gates, bad);
+        std::printf("{\"e2e_cpp\": {\"gates\": %zu, \"devices\": %zu, \"ms\": %.2f, \"bootstraps_per_s\": %.1f, \"pack_ms\": %.2f, "
+                    "\"call_ms\": %.2f, \"unpack_ms\": %.2f}}\n", e2e_gates, be->NumDevices(), best, e2e_gates / (best * 1e-3),
+                    tm.pack_ms, tm.call_ms, tm.unpack_ms);
+    }
+    // ---- keys follow the context: a second BTKeyGen and a second BinFHEContext after RegisterB200 ------------------
+    {
+        auto sk2 = cc.KeyGen();
+        cc.BTKeyGen(sk2);                                  // the context now holds NEW key objects
+        const size_t m = std::min<size_t>(cnt, 6);
+        std::vector<LWECiphertext> x(m), y(m), gpu, cpu(m);
+        for (size_t i = 0; i < m; ++i) { x[i] = cc.Encrypt(sk2, m1[i]); y[i] = cc.Encrypt(sk2, m2[i]); }
+        auto r = EvalBinGateBatch(cc, NAND, x, y, gpu);
+#pragma omp parallel for
+        for (size_t i = 0; i < m; ++i) cpu[i] = cc.EvalBinGate(NAND, x[i], y[i]);
+        size_t bad = r.success ? count_diff(gpu, cpu) : m;
+        for (size_t i = 0; i < m && r.success; ++i) { LWEPlaintext d; cc.Decrypt(sk2, gpu[i], &d); bad += d != (1 - (m1[i] & m2[i])); }
+        report("Rekey_follows_context", m, bad);
+
+        BinFHEContext cc2;                                 // another parameter set in the same process
+        cc2.GenerateBinFHEContext(TOY, ps == TOY && method == GINX ? AP : GINX);
+        auto skb = cc2.KeyGen();
+        cc2.BTKeyGen(skb);
+        std::vector<LWECiphertext> u(m), v(m), g2, c2cpu(m);
+        for (size_t i = 0; i < m; ++i) { u[i] = cc2.Encrypt(skb, m1[i]); v[i] = cc2.Encrypt(skb, m3[i]); }
+        r = EvalBinGateBatch(cc2, OR, u, v, g2);
+        for (size_t i = 0; i < m; ++i) c2cpu[i] = cc2.EvalBinGate(OR, u[i], v[i]);
+        bad = r.success ? count_diff(g2, c2cpu) : m;
+        r = EvalBinGateBatch(cc, NAND, x, y, gpu);         // and back to the first context
+        bad += r.success ? count_diff(gpu, cpu) : m;
+        report("Second_context_rebinds", 2 * m, bad);
+    }
+    if (dcrt) dcrt_check(65536, 32, 60, 2);
+    std::printf("{\"host_parity\": \"%s\", \"devices\": %zu, \"failed_checks\": %d, %s}\n", set.c_str(), be->NumDevices(), g_fail,
+                g_json.c_str());
     return g_fail ? 1 : 0;
 }

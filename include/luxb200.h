@@ -30,6 +30,9 @@
  * the message of the calling thread's last failure.  Host buffers are caller-owned; ciphertext data uses
  * the reference's NativeVector element type (uint64_t, one residue per element).  There is NO CPU fallback:
  * without a CUDA device every compute call fails with LUXB200_ERR_NO_DEVICE.
+ * Threading: a context (one device, one stream, one set of work buffers) serialises its entry points on an internal
+ * mutex, so host threads may share it (the reference's std::async batch futures do); different contexts — e.g. one per
+ * GPU — run concurrently.  An NTT plan is not locked: one thread per plan.
  *
  * Canonical flat key layouts (EVALUATION format, the reference's own coefficient order):
  *   BSK  GINX    [n][2][rows][2][N]              ([i][0] = (*ek)[0][0][i], [i][1] = (*ek)[0][1][i]; rgsw-acc-cggi.cpp:39-57)
@@ -91,11 +94,28 @@ uint64_t luxb200_ksk_len(luxb200_ctx* ctx);   /* elements of KSK A (B has ksk_le
 int luxb200_load_bsk(luxb200_ctx* ctx, const uint64_t* bsk, int on_device);
 int luxb200_load_ksk(luxb200_ctx* ctx, const uint64_t* A, const uint64_t* B, int on_device);
 int luxb200_synchronize(luxb200_ctx* ctx);
+/* One-time key exchange inside one process (the only exchange step of the path): ctxs[0] holds the keys,
+ * ctxs[1..n-1] (same parameters, other GPUs of the box) receive the packed device images peer-to-peer over
+ * NVLink/NVSwitch in ceil(log2 n) doubling rounds.  Multi-process jobs broadcast the canonical arrays with NCCL and load
+ * them with on_device = 1 (fhe_b200/parallel.py). */
+int luxb200_broadcast_keys(luxb200_ctx* const* ctxs, int n);
+/* page-locked host staging for ciphertext batches (so the batch pipeline's copies overlap its kernels) */
+int luxb200_host_alloc(uint64_t bytes, void** out);
+int luxb200_host_free(void* ptr);
 
 /* ---- batched operators, HOST buffers (H2D / D2H inside) ---------------------------------------------- */
 /* a1,a2 [count][n], b1,b2 [count] mod q; out oa [count][n] (or [count][N] mod Q when extended), ob [count] */
 int luxb200_evalbingate_batch(luxb200_ctx* ctx, int gate, const uint64_t* a1, const uint64_t* b1, const uint64_t* a2,
                               const uint64_t* b2, uint64_t* oa, uint64_t* ob, uint64_t count, int extended);
+/* the same with the per-ciphertext semantics of binfhe-base-scheme.cpp:76-126 made explicit: p = plaintext modulus of ct1
+ * (BootstrapGateCore reads it, :535-567); in_ext bit 0 / 1: ct1 / ct2 arrive extended (a [count][N] mod Q) and are run
+ * through SwitchCTtoqn first, as :92-93 does */
+int luxb200_evalbingate_batch_ex(luxb200_ctx* ctx, int gate, const uint64_t* a1, const uint64_t* b1, const uint64_t* a2,
+                                 const uint64_t* b2, uint64_t* oa, uint64_t* ob, uint64_t count, int extended, uint64_t p,
+                                 int in_ext);
+/* LWEEncryptionScheme::SwitchCTtoqn (lwe-pke.cpp:170-178): a [count][N] mod Q, b [count] -> oa [count][n], ob [count] mod q */
+int luxb200_switch_to_qn_batch(luxb200_ctx* ctx, const uint64_t* a, const uint64_t* b, uint64_t* oa, uint64_t* ob,
+                               uint64_t count);
 /* a [count][k][n], b [count][k]; p = plaintext modulus of the inputs (GetptModulus) */
 int luxb200_evalbingate_multi_batch(luxb200_ctx* ctx, int gate, uint32_t k, const uint64_t* a, const uint64_t* b,
                                     uint64_t* oa, uint64_t* ob, uint64_t count, uint64_t p);

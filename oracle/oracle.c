@@ -16,7 +16,8 @@ typedef int64_t i64;
 typedef uint32_t u32;
 typedef unsigned __int128 u128;
 
-static inline u64 mulmod(u64 a, u64 b, u64 q) { return (u64)((u128)a * b % q); }
+/* operands are canonical residues: below 2^32 the product fits in 64 bits (same value, no 128-bit division) */
+static inline u64 mulmod(u64 a, u64 b, u64 q) { return (q >> 32) == 0 ? a * b % q : (u64)((u128)a * b % q); }
 static inline u64 addmod(u64 a, u64 b, u64 q) { u64 s = a + b; return s >= q ? s - q : s; }
 static inline u64 submod(u64 a, u64 b, u64 q) { return a >= b ? a - b : a + q - b; }
 static u64 powmod(u64 a, u64 e, u64 q) {

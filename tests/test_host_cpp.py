@@ -37,18 +37,62 @@ def test_host_layer_refuses_without_gpu():
     assert r.returncode != 0 and "no CPU fallback" in (r.stderr + r.stdout)
 
 
-@pytest.mark.gpu
-@needs_build
-@pytest.mark.parametrize("pset,cnt,pairs", [("TOY", 12, 2), ("TOY_AP", 12, 1), ("TOY_LMKCDEY", 12, 1), ("STD128", 9, 2),
-                                            ("STD128_LMKCDEY", 6, 1), ("STD128_3", 6, 1), ("STD128_4_LMKCDEY", 6, 1)])
-def test_host_layer_matches_reference(pset, cnt, pairs):
-    r = subprocess.run([BIN, pset, str(cnt), str(pairs)], capture_output=True, text=True, timeout=900)
+NEW_CHECKS = ["EvalBinGateBatch_extended_inputs", "EvalBinGateBatch_same_ct_refused", "EvalBinGateBatch_ptmodulus",
+              "Async_overlapping_futures", "Rekey_follows_context", "Second_context_rebinds"]
+
+
+def _run_parity(args, timeout=1500):
+    r = subprocess.run([BIN] + [str(a) for a in args], capture_output=True, text=True, timeout=timeout)
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
     res = json.loads(r.stdout.strip().splitlines()[-1])
     assert res["failed_checks"] == 0
     for k in ["BootstrapBatch", "EvalCMUXBatch", "BatchDAG_levels", "GreaterThan8_circuit", "Backend_BlindRotateBatch",
-              "Backend_ExternalProductBatch", "Backend_KeySwitchBatch", "Backend_ModSwitchBatch", "Backend_PackUnpackBSK"]:
+              "Backend_ExternalProductBatch", "Backend_KeySwitchBatch", "Backend_ModSwitchBatch", "Backend_PackUnpackBSK"] + NEW_CHECKS:
         assert res[k] is True, k
+    return res, r.stdout
+
+
+@pytest.mark.gpu
+@needs_build
+@pytest.mark.parametrize("pset,cnt,pairs", [("TOY", 12, 2), ("TOY_AP", 12, 1), ("TOY_LMKCDEY", 12, 1), ("STD128", 9, 2),
+                                            ("STD128_LMKCDEY", 6, 1), ("STD128_3", 6, 1), ("STD128_4_LMKCDEY", 6, 1),
+                                            ("STD128_AP", 4, 1)])   # STD128_AP: the reference's own 1 GB refresh key
+def test_host_layer_matches_reference(pset, cnt, pairs):
+    _run_parity([pset, cnt, pairs])
+
+
+@pytest.mark.gpu
+@needs_build
+def test_dcrtpoly_switchformat_seam():
+    """host/dcrt_b200: DCRTPoly::SwitchFormat (dcrtpoly-impl.h:1953-1959) at N = 2^16, 32 limbs of 60 bits, every limb of
+    the reference's own DCRTPoly objects, forward and inverse."""
+    res, _ = _run_parity(["TOY", 6, 0, "--dcrt"])
+    assert res["DCRT_SwitchFormat_forward"] is True and res["DCRT_SwitchFormat_inverse"] is True
+
+
+@pytest.mark.gpu
+@needs_build
+def test_evalbingatebatch_e2e_cpp():
+    """the call a reference user makes — lux::fhe::EvalBinGateBatch(cc, AND, vector<LWECiphertext> ...) — on 2^15 gates:
+    every output decrypts to the truth table, the first 64 are bit-identical to cc.EvalBinGate, throughput is printed."""
+    res, out = _run_parity(["STD128", 6, 0, "--e2e", 32768])
+    assert res["e2e_cpp_correct"] is True
+    line = [ln for ln in out.splitlines() if ln.startswith('{"e2e_cpp"')][-1]
+    assert json.loads(line)["e2e_cpp"]["bootstraps_per_s"] > 1000
+
+
+@pytest.mark.gpu
+@needs_build
+def test_multi_device_backend():
+    """one BackendB200 over 2 GPUs (keys copied peer-to-peer with luxb200_broadcast_keys, batches split over the devices):
+    the same parity program, every check, against the live reference.  Needs a 2-GPU box (gpurun --gpus 2)."""
+    from fhe_b200 import lib
+    if lib.load().luxb200_device_count() < 2:
+        pytest.skip("needs 2 GPUs")
+    res, _ = _run_parity(["STD128", 9, 2, "--devices", 2])
+    assert res["devices"] == 2
+    res, _ = _run_parity(["TOY_LMKCDEY", 12, 1, "--devices", 2])
+    assert res["devices"] == 2
 
 
 CAPI = os.path.join(BUILD, "c_api_parity")

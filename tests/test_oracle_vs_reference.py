@@ -59,3 +59,23 @@ def test_toy_gates_bootstrap_func(method):
         r2 = O.orc_evalfunc(oc.h, P(a1), P(b1), P(lut), q, beta, P(xa), P(xb), cnt, q, 4)
         assert r1 == r2 and (r1 != 0 or ((oa == xa).all() and (ob == xb).all()))
     rc.close(); oc.close()
+
+
+def test_dcrt_switchformat_is_per_limb_ntt():
+    """DCRTPolyImpl::SwitchFormat (dcrtpoly-impl.h:1953-1959) of the real reference == the oracle's NTT applied limb by limb
+    with the ILDCRTParams chain (ildcrtparams.h:100-118) — the shape luxb200_ntt_batch is tested against on the GPU."""
+    R, O = orclib.ref(), orclib.oracle()
+    for N, L, bits, cnt in [(4096, 3, 60, 2), (65536, 4, 60, 1), (2048, 2, 50, 2)]:
+        q = np.zeros(L, np.uint64); psi = np.zeros(L, np.uint64); q2 = q.copy(); psi2 = psi.copy()
+        R.ref_dcrt_chain(N, L, bits, P(q), P(psi)); O.orc_dcrt_chain(N, L, bits, P(q2), P(psi2))
+        assert (q == q2).all() and (psi == psi2).all()
+        rng = np.random.default_rng(N + L)
+        x = np.stack([np.stack([rng.integers(0, int(q[l]), size=N, dtype=np.uint64) for l in range(L)]) for _ in range(cnt)])
+        a, b = x.copy(), x.copy()
+        assert R.ref_dcrt_switchformat(N, L, bits, P(a), cnt, 0) == 0
+        for i in range(cnt):
+            for l in range(L):
+                O.orc_ntt(int(q[l]), int(psi[l]), N, P(b[i, l]), 1, 0, 1)
+        assert (a == b).all()
+        assert R.ref_dcrt_switchformat(N, L, bits, P(a), cnt, 1) == 0
+        assert (a == x).all()
