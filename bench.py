@@ -137,7 +137,7 @@ def run_reference(args, rank, world):
         "gpu_launches": 0}))
 
 
-def ntt_metric(lib, local, dev, world, barrier, N=65536, Lm=32, cnt=32, iters=5):
+def ntt_metric(lib, local, dev, world, barrier, N=65536, Lm=32, cnt=32, iters=5, rank0_cpu=False):
     """Batched forward / inverse DCRTPoly NTT (N=2^16, 32 limbs of 60 bits, `cnt` ciphertexts per GPU = 512 MB,
     larger than L2), device-resident, CUDA events on the library stream, max over ranks.  Roofline: the 64-bit
     butterfly rate of luxb200_intpipe_probe64 (integer pipe) and the algorithmic 2*N*8 bytes per limb-NTT (HBM)."""
@@ -149,6 +149,7 @@ def ntt_metric(lib, local, dev, world, barrier, N=65536, Lm=32, cnt=32, iters=5)
         q.append(lib.luxb200_previous_prime(q[-1], 2 * N))
     pl = NTTPlan(N, q, device=local)
     x = torch.randint(0, 2**59, (cnt, Lm, N), dtype=torch.int64, device=dev)
+    x0 = x.clone()
     torch.cuda.synchronize(dev)
     out = {"workload": f"DCRT NTT u64 N={N} L={Lm} x{cnt} per GPU (60-bit primes, {cnt * Lm * N * 8 >> 20} MB > L2)"}
     bf = cnt * Lm * (N // 2) * (N.bit_length() - 1)
@@ -168,13 +169,207 @@ def ntt_metric(lib, local, dev, world, barrier, N=65536, Lm=32, cnt=32, iters=5)
             t = float(tt.item())
         out["inverse" if inv else "forward"] = {"ms": t * 1e3, "Gbutterfly_s": world * bf / t / 1e9,
                                                  "algorithmic_GBs_per_gpu": cnt * Lm * N * 16 / t / 1e9}
+    # parity of the timed buffer: 8 forward then 8 inverse passes must give the input back, and one more forward pass of
+    # ciphertext 0 is compared limb by limb with the oracle (NumberTheoreticTransformNat restatement)
+    ok = bool((x == x0).all().item())
+    kind, orclib = load_checker()
+    O = orclib.oracle()
+    qa = np.array(q, np.uint64); psi = np.zeros(Lm, np.uint64); q2 = np.zeros(Lm, np.uint64)
+    O.orc_dcrt_chain(N, Lm, 60, orclib.P(q2), orclib.P(psi))
+    ok = ok and bool((qa == q2).all())
+    y = x0[:1].clone()
+    ref = y.cpu().numpy().view(np.uint64).copy()
+    pl.SwitchFormatDev(y.data_ptr(), 1, 0, 8); pl.Sync()
+    for l in range(Lm):
+        O.orc_ntt(int(q2[l]), int(psi[l]), N, orclib.P(ref[0, l]), 1, 0, 1)
+    ok = ok and bool((y.cpu().numpy().view(np.uint64) == ref).all())
+    out["parity"] = ok
     pl.close()
     pk = ctypes.c_double(0)
     lib.luxb200_intpipe_probe64(local, ctypes.byref(pk))
-    out["roofline"] = {"bound": "int-pipe (IMAD)", "peak_Gbutterfly_s_per_gpu": pk.value / 1e9,
-                       "frac_forward": out["forward"]["Gbutterfly_s"] / world / (pk.value / 1e9) if pk.value else None,
-                       "frac_inverse": out["inverse"]["Gbutterfly_s"] / world / (pk.value / 1e9) if pk.value else None,
-                       "peak_source": "luxb200_intpipe_probe64: the kernel's own 64-bit Shoup butterfly on registers"}
+    imad, _ = _probe_imad(lib, local)
+    alg = imad / 14.0   # 14 IMAD-pipe issue slots per 64-bit Shoup butterfly: the algorithmic denominator
+    f, i = out["forward"]["Gbutterfly_s"] / world * 1e9, out["inverse"]["Gbutterfly_s"] / world * 1e9
+    out["roofline"] = {"bound": "int-pipe (IMAD)", "peak_Gbutterfly_s_per_gpu": alg / 1e9, "frac_forward": f / alg if alg else None,
+                       "frac_inverse": i / alg if alg else None,
+                       "peak_source": "luxb200_intpipe_probe IMAD rate / 14 issue slots per 64-bit butterfly (algorithmic)",
+                       "own_butterfly_probe": {"peak_Gbutterfly_s_per_gpu": pk.value / 1e9,
+                                               "frac_forward": f / pk.value if pk.value else None,
+                                               "frac_inverse": i / pk.value if pk.value else None,
+                                               "peak_source": "luxb200_intpipe_probe64: the kernel's own compiled butterfly on registers"}}
+    if rank0_cpu:
+        out["cpu_baseline"] = cpu_ntt_baseline(N, int(q2[0]), int(psi[0]), 64, os.cpu_count() or 1)
+    return out
+
+
+def _probe_imad(lib, local):
+    imad = ctypes.c_double(0); mixed = ctypes.c_double(0)
+    lib.luxb200_intpipe_probe(local, ctypes.byref(imad), ctypes.byref(mixed))
+    return imad.value, mixed.value
+
+
+def _peaks():
+    try:
+        return json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        return {}
+
+
+def _traffic(kernel):
+    """DRAM bytes per launch of `kernel` from the tracked ncu capture of this bench command (profiles/r2_traffic.json,
+    written by tools/traffic_from_ncu.py from an `ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum` pass)."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "r2_traffic.json")))
+        k = t["kernels"][kernel]
+        return k["bytes_per_launch"], f"profiles/r2_traffic.json ({t.get('source', '?')}; {k.get('note', '')})"
+    except Exception:
+        return None, "no tracked capture"
+
+
+def cpu_ntt_baseline(N, Q, psi, polys, cores):
+    """the reference's NumberTheoreticTransformNat (lib-benchmark.cpp:151-168 shape) on the host cores,
+    forward, one thread and all threads; bounded sample.  None when the reference library did not travel."""
+    kind, orclib = load_checker()
+    if kind != "reference":
+        return None
+    R = orclib.ref()
+    rng = np.random.default_rng(3)
+    x = rng.integers(0, Q, size=(polys, N), dtype=np.uint64)
+    one = min(polys, max(4, polys // cores))
+    t1 = R.ref_time_ntt(Q, psi, N, orclib.P(x[:one].copy()), one, 0, 1)
+    tn = R.ref_time_ntt(Q, psi, N, orclib.P(x.copy()), polys, 0, cores)
+    bf = (N // 2) * (N.bit_length() - 1)
+    return {"kind": "reference", "unit": "Gbutterfly/s", "one_thread": one * bf / t1 / 1e9, "value": polys * bf / tn / 1e9,
+            "cores": cores, "sample": f"{polys} forward NTTs of N={N} (NativeVector, ChineseRemainderTransformFTT), {tn * 1e3:.1f} ms on {cores} threads, {one} in {t1 * 1e3:.1f} ms on one"}
+
+
+def ntt32_metric(lib, local, dev, N, bits, count=65536, iters=10):
+    """BASELINE configs[1]: `count` polynomials of the binfhe modulus, u32 warp-per-polynomial kernel, device-resident,
+    CUDA events on the plan stream.  HBM roofline: algorithmic 2*N*4 bytes per transform against MEASURED_PEAKS hbm_gbs.
+    Parity of the timed buffer: round trip back to the input after equally many forward and inverse passes, and one more
+    forward pass of 64 polynomials against the oracle."""
+    import torch
+    from fhe_b200.context import NTTPlan
+    Q = lib.luxb200_last_prime(bits, 2 * N)
+    pl = NTTPlan(N, [Q], device=local)
+    x = torch.randint(0, Q, (count, N), dtype=torch.int32, device=dev)
+    x0 = x.clone()
+    torch.cuda.synchronize(dev)
+    peaks = _peaks()
+    hbm = peaks.get("hbm_gbs", 6550.0)
+    out = {"workload": f"batched NTT u32 N={N} Q={bits}-bit x{count} ({count * N * 4 >> 20} MB > L2)", "bound": "hbm",
+           "peak_gbs": hbm, "peak_source": "MEASURED_PEAKS.json hbm_gbs" if "hbm_gbs" in peaks else "fallback"}
+    for inv in (0, 1):
+        for _ in range(3):
+            pl.SwitchFormatDev(x.data_ptr(), count, inv, 4)
+        pl.Sync()
+        ms = []
+        for _ in range(iters):
+            pl.SwitchFormatDev(x.data_ptr(), count, inv, 4)
+            ms.append(pl.LastMs())
+        t = float(np.median(ms)) * 1e-3
+        gbs = count * N * 4 * 2 / t / 1e9
+        out["inverse" if inv else "forward"] = {"ms": t * 1e3, "Gbutterfly_s": count * (N // 2) * (N.bit_length() - 1) / t / 1e9,
+                                                 "algorithmic_GBs": gbs, "frac_hbm": gbs / hbm}
+    ok = bool((x == x0).all().item())
+    kind, orclib = load_checker()
+    O = orclib.oracle()
+    psi = O.orc_root_of_unity(2 * N, Q)
+    sample = x0[:64].cpu().numpy().view(np.uint32).astype(np.uint64)
+    ref = sample.copy(); O.orc_ntt(Q, psi, N, orclib.P(ref), 64, 0, 8)
+    y = x0[:64].clone()
+    pl.SwitchFormatDev(y.data_ptr(), 64, 0, 4); pl.Sync()
+    ok = ok and bool((y.cpu().numpy().view(np.uint32).astype(np.uint64) == ref).all())
+    out["parity"] = ok
+    out["cpu_baseline"] = cpu_ntt_baseline(N, Q, psi, 4096, os.cpu_count() or 1)
+    pl.close()
+    return out
+
+
+def _lmkcdey_ops(a, q, N, w):
+    """(external products, automorphisms) of one LMKCDEY blind rotation, counted as rgsw-acc-lmkcdey.cpp:83-157 walks it:
+    masks are bucketed by log_5 of (-a_i | 1) mod 2N; the two sweeps i = N/2-1 .. 1 emit an automorphism before every
+    occupied bucket that follows skipped ones and after every `w` skips."""
+    M, Nh = 2 * N, N // 2
+    assert q == M, "op count written for q = 2N (STD128_LMKCDEY)"
+    table, gp = {1: (0, 1), M - 1: (0, -1)}, 1
+    for i in range(1, Nh):
+        gp = (gp * 5) % M
+        table[gp] = (i, 1); table[M - gp] = (i, -1)
+    occ = {1: set(), -1: set()}
+    for ai in a:
+        ai = int(ai) % q
+        i, sgn = table[((0 if ai == 0 else M - ai) | 1) % M]
+        occ[sgn].add(i)
+    autos = 0
+    for sgn in (-1, 1):
+        skips = 0
+        for i in range(Nh - 1, 0, -1):
+            if i in occ[sgn] and skips != 0:
+                autos += 1; skips = 0
+            skips += 1
+            if skips == w or i == 1:
+                autos += 1; skips = 0
+    return len(a), autos + 1   # + the automorphism by 2N - 5 between the sweeps
+
+
+def method_metric(lib, local, dev, name, method, G, imad_peak):
+    """BASELINE configs[3] shapes: G gates of STD128_LMKCDEY / STD128_AP through the scheduled blind-rotation kernel.
+    value = device-timed gates/s of the whole call's kernels, e2e = host buffers through the C ABI.  Roofline of
+    br_sched_kernel against the live IMAD probe with the algorithmic count written out: per external product 6 transforms
+    x 5120 butterflies x 3 IMAD + 8 x 1024 pointwise x 4 IMAD = 124 928; per LMKCDEY automorphism 3 x 5120 x 3 + 4 x 1024 x 4 =
+    62 464; op counts are those of the timed inputs (AP: non-zero base-baseR digits of -a_i; LMKCDEY: a sample of 256 op
+    lists re-derived on the host)."""
+    from fhe_b200 import keygen as kg
+    from fhe_b200.context import BinFHEContext
+    ctx = BinFHEContext(device=local).GenerateBinFHEContext(name, method)
+    ks = kg.keygen(ctx, seed=77)
+    ctx.BTKeyLoad(ks.bsk, ks.kskA, ks.kskB)
+    rng = np.random.default_rng(5)
+    m1 = rng.integers(0, 2, G); m2 = rng.integers(0, 2, G)
+    a1, b1 = kg.encrypt(ctx, ks.sk, m1, rng); a2, b2 = kg.encrypt(ctx, ks.sk, m2, rng)
+    for _ in range(2):
+        ctx.EvalBinGateBatch("AND", (a1[:1024], b1[:1024]), (a2[:1024], b2[:1024]))
+    br = tot = wall = 0.0
+    reps = 3
+    for _ in range(reps):
+        t0 = time.perf_counter()
+        (oa, ob), res = ctx.EvalBinGateBatch("AND", (a1, b1), (a2, b2))
+        wall += time.perf_counter() - t0
+        assert res.success, res.error
+        tm = ctx.LastTiming()
+        br += tm["br_ms"]; tot += tm["total_ms"]
+    errors = int((kg.decrypt(ctx, ks.sk, oa, ob) != (m1 & m2)).sum())
+    s = (a1 + a2) % ctx.q          # the blind rotation runs on ct1 + ct2 (AND)
+    EXT, AUTO = 6 * 5120 * 3 + 8 * 1024 * 4, 3 * 5120 * 3 + 4 * 1024 * 4
+    if method == "AP":
+        neg = (ctx.q - s) % ctx.q
+        ops = sum(int(((neg // (ctx.baseR ** k)) % ctx.baseR != 0).sum()) for k in range(ctx.digitsR)) / G
+        imad = ops * EXT
+        counts = {"external_products_per_gate": ops, "automorphisms_per_gate": 0}
+    else:
+        sample = [_lmkcdey_ops(s[i], ctx.q, ctx.N, ctx.numAutoKeys) for i in range(0, G, max(1, G // 256))]
+        ne = float(np.mean([x[0] for x in sample])); na = float(np.mean([x[1] for x in sample]))
+        imad = ne * EXT + na * AUTO
+        counts = {"external_products_per_gate": ne, "automorphisms_per_gate": na}
+    br_s = br * 1e-3 / reps
+    achieved = G * imad / br_s
+    out = {"workload": f"{name} EvalBinGate(AND) x{G}", "value": G / (tot * 1e-3 / reps), "unit": "bootstraps/s",
+           "e2e": {"value": G * reps / wall, "unit": "bootstraps/s"}, "decrypt_errors": errors,
+           "roofline": {"bound": "int32-pipe", "kernel": "br_sched_kernel", "achieved": achieved / 1e12, "peak": imad_peak / 1e12,
+                        "unit": "TIMAD/s", "frac": achieved / imad_peak if imad_peak else None,
+                        "algorithmic_imad_per_gate": imad, "imad_per_external_product": EXT, "imad_per_automorphism": AUTO,
+                        "kernel_ms": br_s * 1e3, **counts}}
+    if method == "AP":
+        # SURVEY 8(d) expected the key gather to bind AP: bytes of RGSW keys the op lists touch / kernel time vs HBM
+        kb = counts["external_products_per_gate"] * ctx.rows * 2 * ctx.N * 4 * G
+        peaks = _peaks()
+        out["roofline"]["key_stream_GBs_if_from_hbm"] = kb / br_s / 1e9
+        out["roofline"]["hbm_peak_gbs"] = peaks.get("hbm_gbs")
+        out["roofline"]["note"] = ("even if every key byte the op lists touch came from DRAM the stream would need about a third of "
+                                   "the HBM peak; the CTAs walk i together, so most of the 1 GB key is served from L2 (ncu "
+                                   "r1_sched_ap_v0: L2 hit 93 %): the integer pipe binds, not HBM (SURVEY 8(d) expected HBM)")
+    ctx.close()
     return out
 
 
@@ -189,6 +384,8 @@ def main():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-ntt", action="store_true")
+    ap.add_argument("--no-strong", action="store_true")
+    ap.add_argument("--no-extras", action="store_true")
     args = ap.parse_args()
     rank, local, world = env_int("RANK", 0), env_int("LOCAL_RANK", 0), env_int("WORLD_SIZE", 1)
 
@@ -295,7 +492,11 @@ def main():
     oa = d_oa[:half].cpu().numpy().view(np.uint32).astype(np.uint64)
     ob = d_ob[:half].cpu().numpy().view(np.uint32).astype(np.uint64)
     dec = kg.decrypt(ctx, sk, oa, ob)
-    errors = int((dec != (m1 & m2)).sum())
+    errors = int((dec != (m1 & m2)).sum())       # every rank decrypts the encrypted half of ITS shard
+    if world > 1:
+        te = torch.tensor([errors], dtype=torch.int64, device=dev)
+        dist.all_reduce(te)                         # summed over ranks before rank 0 prints
+        errors = int(te.item())
 
     # ---- e2e through the host-buffer C ABI call (pinned host memory, H2D + D2H inside)
     e2e = None
@@ -319,7 +520,47 @@ def main():
     # ---- second headline metric: DCRT RNS NTT at N=2^16, 32 x 60-bit limbs (BASELINE configs[4]), weak-scaled
     ntt = None
     if not args.no_ntt:
-        ntt = ntt_metric(lib, local, dev, world, barrier)
+        ntt = ntt_metric(lib, local, dev, world, barrier, rank0_cpu=(rank == 0 and world == 1 and not args.no_cpu_baseline))
+
+    # ---- BASELINE configs[2] as written: 2^16 gates TOTAL, sharded over the N GPUs (strong scaling; the headline above is
+    # the weak curve, 2^16 per GPU).  parallel.shard_range gives each rank its contiguous slice of the same inputs.
+    strong = None
+    if not args.no_strong:
+        from fhe_b200 import parallel as par
+        TOT = 65536
+        lo, hi = par.shard_range(TOT, rank, world)
+        m = hi - lo
+        sl = [x[:m].contiguous() for x in d]
+        hs = [x[:m] for x in h]
+        so_a = d_oa[:m]; so_b = d_ob[:m]
+
+        def s_dev():
+            ctx.EvalBinGateBatchDev("AND", sl[0].data_ptr(), sl[1].data_ptr(), sl[2].data_ptr(), sl[3].data_ptr(),
+                                    so_a.data_ptr(), so_b.data_ptr(), m)
+
+        def s_e2e():
+            from fhe_b200 import lib as _l
+            _l.check(lib.luxb200_evalbingate_batch(ctx.h, _l.GATE["AND"], _l.VP(hs[0].data_ptr()), _l.VP(hs[1].data_ptr()),
+                                                   _l.VP(hs[2].data_ptr()), _l.VP(hs[3].data_ptr()), _l.VP(h_oa.data_ptr()),
+                                                   _l.VP(h_ob.data_ptr()), m, 0))
+        res = {}
+        for nm, fn in (("value", s_dev), ("e2e", s_e2e)):
+            fn(); ctx.Synchronize()
+            barrier()
+            t0 = time.perf_counter()
+            for _ in range(args.steps):
+                fn()
+            ctx.Synchronize()
+            barrier()
+            t = time.perf_counter() - t0
+            if world > 1:
+                tt = torch.tensor([t], dtype=torch.float64, device=dev)
+                dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+                t = float(tt.item())
+            res[nm] = TOT * args.steps / t
+        strong = {"workload": f"{TOT} STD128 GINX AND gates in total, {m} per GPU (parallel.shard_range)", "scaling": "strong",
+                  "value": res["value"], "e2e": res["e2e"], "unit": "bootstraps/s", "gates_per_gpu": m,
+                  "waves_per_gpu": m / 888.0}
 
     if rank != 0:
         if world > 1:
@@ -327,24 +568,32 @@ def main():
         return
 
     # ---- roofline of the dominant kernel (fused blind rotation): integer-pipe bound
-    imad = ctypes.c_double(0); mixed = ctypes.c_double(0)
-    lib.luxb200_intpipe_probe(local, ctypes.byref(imad), ctypes.byref(mixed))
+    imad_v, mixed_v = _probe_imad(lib, local)
     br_s = br_ms * 1e-3 / args.steps
     achieved = G * IMAD_PER_GATE / br_s
-    peaks = {}
-    try:
-        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
-    except Exception:
-        pass
-    roofline = {"bound": "int32-pipe", "kernel": "br_ginx_kernel", "achieved": achieved / 1e12, "peak": imad.value / 1e12,
-                "unit": "TIMAD/s", "frac": achieved / imad.value if imad.value else None,
-                # DRAM bytes of one br_ginx launch at this batch size, from the ncu pass in profiles/r1_launches_v3.csv
-                # (196 MB read + 252 MB written; algorithmic: 132 MB masks + 269 MB extracted cts + 41 MB keys/monomials)
-                "traffic": 438.7e6 if G == 65536 else None, "traffic_unit": "bytes/launch (profiles/r1_launches_v3.csv: 189.3 MB read + 249.4 MB written)",
+    peaks = _peaks()
+    traffic, traffic_src = _traffic("br_ginx_kernel") if G == 65536 else (None, "only captured for 65536 gates")
+    roofline = {"bound": "int32-pipe", "kernel": "br_ginx_kernel", "achieved": achieved / 1e12, "peak": imad_v / 1e12,
+                "unit": "TIMAD/s", "frac": achieved / imad_v if imad_v else None,
+                # DRAM bytes of one br_ginx launch at this batch size (algorithmic: 132 MB masks + 269 MB extracted
+                # ciphertexts + 41 MB keys/monomials = 442 MB)
+                "traffic": traffic, "traffic_source": traffic_src,
                 "peak_source": "luxb200_intpipe_probe (dependent IMAD chains, measured live on this GPU)",
                 "algorithmic_imad_per_gate": IMAD_PER_GATE, "kernel_ms_per_step": br_ms / args.steps,
                 "kernel_share_of_step": br_ms * 1e-3 / t_dev,
-                "butterfly_peak_per_s": mixed.value, "hbm_peak_gbs": peaks.get("hbm_gbs")}
+                "butterfly_peak_per_s": mixed_v, "hbm_peak_gbs": peaks.get("hbm_gbs")}
+
+    # ---- the other BASELINE configs, N = 1 only (a few steps each, after the headline): configs[1] u32 NTT batches,
+    # configs[3] LMKCDEY / AP gates.  Each carries its own roofline fraction.
+    extras = {}
+    if world == 1 and not args.no_extras:
+        ctx.close()
+        del d, d_oa, d_ob
+        torch.cuda.empty_cache()
+        extras["ntt32_n1024"] = ntt32_metric(lib, local, dev, 1024, 27)
+        extras["ntt32_n2048"] = ntt32_metric(lib, local, dev, 2048, 29)
+        extras["lmkcdey"] = method_metric(lib, local, dev, "STD128_LMKCDEY", "LMKCDEY", 16384, imad_v)
+        extras["ap"] = method_metric(lib, local, dev, "STD128_AP", "AP", 4096, imad_v)
 
     cpu_baseline = None
     if not args.no_cpu_baseline:
@@ -365,7 +614,9 @@ def main():
                    "global_gates": G * world, "n": n, "N": ctx.N, "Q": ctx.Q, "parallelism": f"batch-shard x{world}",
                    "l2": "working set per step (inputs 264 MB, extracted cts 269 MB, KSK 100 MB) exceeds the 126 MB L2"},
         "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches), "roofline": roofline,
-        "cpu_baseline": cpu_baseline, "ntt_n65536": ntt, "decrypt_errors": errors, "br_ms_per_step": br_ms / args.steps,
+        "cpu_baseline": cpu_baseline, "ntt_n65536": ntt, "strong_2p16": strong, **extras,
+        "decrypt_errors": errors, "decrypt_errors_scope": f"encrypted half of every rank's shard, summed over {world} rank(s)",
+        "br_ms_per_step": br_ms / args.steps,
         "ks_ms_per_step": ks_ms / args.steps,
         # CUDA events on the library stream around every kernel of the step (prep + blind rotation + key switch), rank 0;
         # `value` uses the wall clock between the two barrier + synchronize brackets (max over ranks), which contains it

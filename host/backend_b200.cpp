@@ -535,14 +535,17 @@ void BackendB200::UnpackCiphertexts(const DeviceBuffer& packed, std::vector<LWEC
 }
 
 // ---- gate-level entry points (BinFHEScheme::EvalBinGate / Bootstrap / EvalFunc, binfhe-base-scheme.cpp:76-332) --
-// One homogeneous group of 2-input gates: every ct1 has plaintext modulus p and one format, every ct2 one format.
+// One homogeneous group of 2-input gates: every ct1 one format (SMALL_DIM or extended), every ct2 one format.
+// The plaintext modulus handed to the device is always 4: EvalBinGate bootstraps a COPY of ct1 (binfhe-base-scheme.cpp:92)
+// and LWECiphertextImpl's copy constructor does not carry m_p (lwe-ciphertext.h:56), so whatever ct1->GetptModulus() says,
+// BootstrapGateCore sees 4 (host_parity "EvalBinGateBatch_ptmodulus" checks exactly this against the reference).
 void BackendB200::gate2(BINGATE gate, const std::vector<LWECiphertext>& ct1, const std::vector<LWECiphertext>& ct2,
                         std::vector<LWECiphertext>& out) {
     const size_t cnt = ct1.size();
     const uint32_t n = p_.n, N = p_.N;
     const bool e1 = u64(ct1[0]->GetModulus()) == p_.Q, e2 = u64(ct2[0]->GetModulus()) == p_.Q;   // binfhe-base-scheme.cpp:92-93
     const uint32_t l1 = e1 ? N : n, l2 = e2 ? N : n;
-    const uint64_t pm = u64(ct1[0]->GetptModulus());
+    const uint64_t pm = 4;
     const double t0 = now_ms();
     uint64_t *a1 = st_[0].ensure(cnt * size_t(l1)), *b1 = st_[1].ensure(cnt), *a2 = st_[2].ensure(cnt * size_t(l2)),
              *b2 = st_[3].ensure(cnt), *oa = st_[4].ensure(cnt * size_t(n)), *ob = st_[5].ensure(cnt);
@@ -566,21 +569,19 @@ void BackendB200::EvalBinGate(BINGATE gate, const std::vector<LWECiphertext>& ct
     if (ct1.size() != ct2.size()) throw std::invalid_argument("Input size mismatch");
     if (ct1.empty()) { out.clear(); return; }
     std::lock_guard<std::recursive_mutex> lk(mu_);
-    // per-element checks of BinFHEScheme::EvalBinGate (binfhe-base-scheme.cpp:81-86) and the properties one device call
-    // shares across its batch: plaintext modulus of ct1 and the SMALL_DIM / extended format of either operand
+    // per-element checks of BinFHEScheme::EvalBinGate (binfhe-base-scheme.cpp:81-86) and the property one device call
+    // shares across its batch: the SMALL_DIM / extended format of either operand
     bool uniform = true;
     for (size_t i = 0; i < ct1.size(); ++i) {
         if (!ct1[i]) throw std::invalid_argument("Ciphertext1 is empty");
         if (!ct2[i]) throw std::invalid_argument("Ciphertext2 is empty");
         if (ct1[i] == ct2[i]) throw std::invalid_argument("Input ciphertexts should be independant");
-        uniform = uniform && ct1[i]->GetptModulus() == ct1[0]->GetptModulus() && ct1[i]->GetModulus() == ct1[0]->GetModulus() &&
-                  ct2[i]->GetModulus() == ct2[0]->GetModulus();
+        uniform = uniform && ct1[i]->GetModulus() == ct1[0]->GetModulus() && ct2[i]->GetModulus() == ct2[0]->GetModulus();
     }
     if (uniform) { gate2(gate, ct1, ct2, out); return; }
-    // mixed batch: one device call per (p, format of ct1, format of ct2) group, results scattered back in order
-    std::map<std::tuple<uint64_t, uint64_t, uint64_t>, std::vector<size_t>> groups;
-    for (size_t i = 0; i < ct1.size(); ++i)
-        groups[{u64(ct1[i]->GetptModulus()), u64(ct1[i]->GetModulus()), u64(ct2[i]->GetModulus())}].push_back(i);
+    // mixed batch: one device call per (format of ct1, format of ct2) group, results scattered back in order
+    std::map<std::pair<uint64_t, uint64_t>, std::vector<size_t>> groups;
+    for (size_t i = 0; i < ct1.size(); ++i) groups[{u64(ct1[i]->GetModulus()), u64(ct2[i]->GetModulus())}].push_back(i);
     out.assign(ct1.size(), nullptr);
     for (const auto& g : groups) {
         std::vector<LWECiphertext> x, y, r;

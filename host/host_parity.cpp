@@ -436,13 +436,19 @@ int main(int argc, char** argv) {
         std::vector<LWECiphertext> o;
         r = EvalBinGateBatch(cc, AND, c1, c1, o);
         report("EvalBinGateBatch_same_ct_refused", 1, (!r.success && r.error.find("independant") != std::string::npos) ? 0 : 1);
-        // (c) the plaintext modulus of ct1 reaches the test vector (BootstrapGateCore, :535-567)
+        // (c) a ct1 that claims plaintext modulus 8: the reference bootstraps a COPY of it, and the copy constructor drops m_p
+        // (lwe-ciphertext.h:56), so the result is that of p = 4 — and Bootstrap() mixes both (table with 4, offset with p)
         std::vector<LWECiphertext> p8(m);
         for (size_t i = 0; i < m; ++i) { p8[i] = std::make_shared<LWECiphertextImpl>(*c1[i]); p8[i]->SetptModulus(NativeInteger(8)); }
         r = EvalBinGateBatch(cc, OR, p8, y, gpu);
 #pragma omp parallel for
         for (size_t i = 0; i < m; ++i) cpu[i] = cc.EvalBinGate(OR, p8[i], y[i]);
-        report("EvalBinGateBatch_ptmodulus", m, r.success ? count_diff(gpu, cpu) : m);
+        size_t badp = r.success ? count_diff(gpu, cpu) : m;
+        r = BootstrapBatch(cc, p8, gpu);
+#pragma omp parallel for
+        for (size_t i = 0; i < m; ++i) cpu[i] = cc.Bootstrap(p8[i]);
+        badp += r.success ? count_diff(gpu, cpu) : m;
+        report("EvalBinGateBatch_ptmodulus", 2 * m, badp);
     }
     // ---- two async futures in flight on one backend (batch.cpp:320-349 runs them on std::async threads) -----------
     {
@@ -488,6 +494,7 @@ int main(int argc, char** argv) {
     // ---- keys follow the context: a second BTKeyGen and a second BinFHEContext after RegisterB200 ------------------
     {
         auto sk2 = cc.KeyGen();
+        cc.ClearBTKeys();                                  // (a second BTKeyGen alone re-uses the cached map entry)
         cc.BTKeyGen(sk2);                                  // the context now holds NEW key objects
         const size_t m = std::min<size_t>(cnt, 6);
         std::vector<LWECiphertext> x(m), y(m), gpu, cpu(m);

@@ -107,9 +107,10 @@ int luxb200_host_free(void* ptr);
 /* a1,a2 [count][n], b1,b2 [count] mod q; out oa [count][n] (or [count][N] mod Q when extended), ob [count] */
 int luxb200_evalbingate_batch(luxb200_ctx* ctx, int gate, const uint64_t* a1, const uint64_t* b1, const uint64_t* a2,
                               const uint64_t* b2, uint64_t* oa, uint64_t* ob, uint64_t count, int extended);
-/* the same with the per-ciphertext semantics of binfhe-base-scheme.cpp:76-126 made explicit: p = plaintext modulus of ct1
- * (BootstrapGateCore reads it, :535-567); in_ext bit 0 / 1: ct1 / ct2 arrive extended (a [count][N] mod Q) and are run
- * through SwitchCTtoqn first, as :92-93 does */
+/* the same with the per-ciphertext semantics of binfhe-base-scheme.cpp:76-126 made explicit: p = plaintext modulus the
+ * test vector is built for (BootstrapGateCore, :535-567; the reference itself always ends up with 4 here because it
+ * bootstraps a copy of ct1 and the copy constructor drops m_p); in_ext bit 0 / 1: ct1 / ct2 arrive extended (a [count][N]
+ * mod Q) and are run through SwitchCTtoqn first, as :92-93 does */
 int luxb200_evalbingate_batch_ex(luxb200_ctx* ctx, int gate, const uint64_t* a1, const uint64_t* b1, const uint64_t* a2,
                                  const uint64_t* b2, uint64_t* oa, uint64_t* ob, uint64_t count, int extended, uint64_t p,
                                  int in_ext);

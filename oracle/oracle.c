@@ -709,7 +709,9 @@ int orc_bootstrap(OrcCtx* c, const u64* a, const u64* b, u64* oa, u64* ob, u64 c
     for (u64 i = 0; i < count; ++i) {
         u64* lut = malloc(sizeof(u64) * (q + N + 1));
         u64* ext = lut + q;
-        gate_lut(c, ORC_AND, q, p, lut);
+        /* BootstrapGateCore gets a COPY of ct (:200) and the copy constructor drops m_p (lwe-ciphertext.h:56):
+         * the table is built with p = 4; the caller's p only enters the offset (:214) */
+        gate_lut(c, ORC_AND, q, 4, lut);
         orc_bootstrap_core(c, a + i * n, addmod(b[i], q >> 2, q), q, lut, ext);
         gate_finish(c, ext, p, extended, oa + i * on, ob + i);
         free(lut);

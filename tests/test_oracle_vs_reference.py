@@ -51,6 +51,11 @@ def test_toy_gates_bootstrap_func(method):
     R.ref_bootstrap(rc.h, P(a1), P(b1), P(oa), P(ob), cnt, 4, 0, 4)
     O.orc_bootstrap(oc.h, P(a1), P(b1), P(xa), P(xb), cnt, 4, 0, 4)
     assert (oa == xa).all() and (ob == xb).all()
+    # a ciphertext that claims plaintext modulus 8: the table is still built for 4 (the copy at binfhe-base-scheme.cpp:200
+    # drops m_p), the offset uses 8 (:214)
+    R.ref_bootstrap(rc.h, P(a1), P(b1), P(oa), P(ob), cnt, 8, 0, 4)
+    O.orc_bootstrap(oc.h, P(a1), P(b1), P(xa), P(xb), cnt, 8, 0, 4)
+    assert (oa == xa).all() and (ob == xb).all()
     q, beta = p.q, R.ref_get_beta(rc.h)
     pp = max(2, q // (2 * beta)); step = q // pp
     for f in (lambda m: m % (pp // 2), lambda m: (m * m * m) % pp):
