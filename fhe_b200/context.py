@@ -33,7 +33,37 @@ PARAM_SETS = {
     "STD128_4_LMKCDEY": (27, 2048, 595, 2048, 65536, 64, 128, 64, 10, 0),
     "STD128Q_LMKCDEY": (27, 2048, 483, 2048, 16384, 32, 512, 64, 10, 1),
     "STD128Q_3_LMKCDEY": (25, 2048, 643, 2048, 65536, 64, 128, 64, 10, 0),
+    # N = 2048 and / or Q above 2^30: the shared-memory blind rotation (csrc/br_wide.cuh)
+    "STD128Q_3": (50, 4096, 600, 2048, 32768, 32, 33554432, 64, 10, 0),
+    "STD128Q_4": (50, 4096, 641, 2048, 65536, 64, 33554432, 64, 10, 0),
+    "STD192": (37, 4096, 790, 2048, 16384, 32, 524288, 64, 10, 0),
+    "STD192_3": (37, 4096, 875, 4096, 65536, 64, 524288, 64, 10, 0),
+    "STD192_4": (37, 4096, 875, 4096, 65536, 64, 8192, 64, 10, 0),
+    "STD192Q": (35, 4096, 875, 1024, 32768, 32, 4096, 32, 10, 0),
+    "STD192Q_3": (34, 4096, 922, 2048, 65536, 16, 4096, 64, 10, 0),
+    "STD192Q_4": (34, 4096, 980, 2048, 131072, 16, 4096, 64, 10, 0),
+    "STD256": (29, 4096, 1076, 2048, 32768, 32, 1024, 64, 10, 0),
+    "STD256_3": (29, 4096, 1145, 2048, 65536, 64, 256, 64, 10, 0),
+    "STD256_4": (29, 4096, 1145, 4096, 65536, 64, 256, 64, 10, 0),
+    "STD256Q": (27, 4096, 1225, 1024, 65536, 16, 128, 32, 10, 0),
+    "STD256Q_3": (27, 4096, 1400, 4096, 65536, 21, 64, 64, 10, 0),
+    "STD256Q_4": (27, 4096, 1625, 4096, 2097152, 16, 64, 64, 10, 0),
+    "STD128Q_4_LMKCDEY": (50, 4096, 641, 4096, 65536, 64, 33554432, 64, 10, 0),
+    "STD192_LMKCDEY": (39, 4096, 716, 2048, 32768, 32, 1048576, 64, 10, 1),
+    "STD192_3_LMKCDEY": (39, 4096, 771, 4096, 65536, 64, 1048576, 64, 10, 1),
+    "STD192_4_LMKCDEY": (37, 4096, 875, 4096, 65536, 64, 8192, 64, 10, 0),
+    "STD192Q_LMKCDEY": (36, 4096, 776, 4096, 32768, 32, 262144, 64, 10, 1),
+    "STD192Q_3_LMKCDEY": (36, 4096, 834, 4096, 65536, 64, 4096, 64, 10, 1),
+    "STD192Q_4_LMKCDEY": (34, 4096, 949, 4096, 65536, 64, 4096, 64, 10, 0),
+    "STD256_LMKCDEY": (30, 4096, 939, 2048, 32768, 32, 1024, 64, 10, 1),
+    "STD256_3_LMKCDEY": (29, 4096, 1076, 4096, 32768, 32, 256, 64, 10, 0),
+    "STD256_4_LMKCDEY": (29, 4096, 1145, 4096, 65536, 64, 256, 64, 10, 0),
+    "STD256Q_LMKCDEY": (28, 4096, 1019, 4096, 32768, 32, 1024, 64, 10, 1),
+    "STD256Q_3_LMKCDEY": (26, 4096, 1242, 4096, 65536, 64, 128, 64, 10, 0),
+    "STD256Q_4_LMKCDEY": (26, 4096, 1320, 4096, 131072, 64, 64, 64, 10, 0),
     "LPF_STD128": (27, 2048, 556, 2048, 32768, 32, 128, 64, 10, 0),
+    "LPF_STD128Q": (25, 2048, 645, 2048, 65536, 64, 128, 64, 10, 0),
+    "LPF_STD128Q_LMKCDEY": (25, 2048, 600, 2048, 32768, 32, 128, 64, 10, 0),
     "LPF_STD128_LMKCDEY": (27, 2048, 556, 2048, 32768, 32, 512, 64, 10, 0),
     "SIGNED_MOD_TEST": (28, 2048, 512, 1024, PRIME, 25, 128, 23, 10, 0),
 }

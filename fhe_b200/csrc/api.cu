@@ -4,6 +4,7 @@
 #include "api_common.h"
 #include "aux_kernels.cuh"
 #include "br_sched.cuh"
+#include "br_wide.cuh"
 #include "ntt_kernels.cuh"
 
 thread_local std::string g_last_error;
@@ -102,10 +103,10 @@ int luxb200_ctx_create(const luxb200_params* p, int device, luxb200_ctx** out) {
     if (p->method < LUXB200_AP || p->method > LUXB200_LMKCDEY) return lb_fail(LUXB200_ERR_INVALID_ARG, "bad method %u", p->method);
     if (p->baseG == 0 || (p->baseG & (p->baseG - 1))) return lb_fail(LUXB200_ERR_INVALID_ARG, "Gadget base should be a power of two.");
     if (p->q == 0 || (p->q & (p->q - 1)) || (2ull * p->N) % p->q) return lb_fail(LUXB200_ERR_INVALID_ARG, "q must be a power of two dividing 2N");
-    if (p->Q >= (1ull << 30) || !is_prime(p->Q) || (p->Q - 1) % (2ull * p->N))
-        return lb_fail(LUXB200_ERR_UNSUPPORTED, "Q must be an NTT prime below 2^30 on the u32 bootstrapping path");
-    if (p->qKS >= (1ull << 32)) return lb_fail(LUXB200_ERR_UNSUPPORTED, "qKS must fit in 32 bits");
-    if (p->N > 1024) return lb_fail(LUXB200_ERR_UNSUPPORTED, "blind rotation kernels are built for N <= 1024 (got %u)", p->N);
+    if (p->Q >= (1ull << 60) || !is_prime(p->Q) || (p->Q - 1) % (2ull * p->N))
+        return lb_fail(LUXB200_ERR_UNSUPPORTED, "Q must be an NTT prime below 2^60");
+    if (p->N > 4096) return lb_fail(LUXB200_ERR_UNSUPPORTED, "blind rotation kernels are built for N <= 4096 (got %u)", p->N);
+    if (p->baseKS < 2) return lb_fail(LUXB200_ERR_INVALID_ARG, "baseKS must be at least 2");
     LB_TRY(lb_set_device(device));
     luxb200_ctx* c = new luxb200_ctx();
     c->p = *p;
@@ -116,7 +117,57 @@ int luxb200_ctx_create(const luxb200_params* p, int device, luxb200_ctx** out) {
     c->digitsR = digit_count(p->q, p->baseR ? p->baseR : 2);
     c->rows = 2 * (c->digitsG - 1);
     if (c->p.psi == 0) c->p.psi = root_of_unity(2ull * p->N, p->Q);
-    if (c->rows != 4 && c->rows != 6 && c->rows != 2) { luxb200_ctx_destroy(c); return lb_fail(LUXB200_ERR_UNSUPPORTED, "digitsG-1 = %u not supported", c->rows / 2); }
+    if (c->digitsG < 2 || c->digitsG > 9) { luxb200_ctx_destroy(c); return lb_fail(LUXB200_ERR_UNSUPPORTED, "digitsG = %u not supported", c->digitsG); }
+    // column sums of the key switch: N * digitsKS entries below qKS must fit the 64-bit accumulator
+    if ((u128_t)p->qKS * p->N * c->digitsKS >= ((u128_t)1 << 64)) { luxb200_ctx_destroy(c); return lb_fail(LUXB200_ERR_UNSUPPORTED, "qKS too large for the key-switch accumulator"); }
+    // the register-resident warp-pair kernels cover N = 1024 with 2 or 3 digits and N = 512 with 2, Q < 2^30; everything else
+    // (N = 2048, 64-bit Q, 1 / 4 / 5 digits) runs the shared-memory kernel of br_wide.cuh
+    const bool fast = p->Q < (1ull << 30) && ((c->logN == 10 && (c->rows == 4 || c->rows == 6)) || (c->logN == 9 && c->rows == 4));
+    c->wide.on = !fast;
+    if (c->wide.on) {
+        luxb200_ctx::Wide& W = c->wide;
+        W.wsize = p->Q < (1ull << 30) ? 4 : 8;
+        const uint32_t N = p->N;
+        W.smem = (size_t)(2 + c->rows) * (N + N / 16) * W.wsize;
+        if (W.smem > 232448 || N < 256) { luxb200_ctx_destroy(c); return lb_fail(LUXB200_ERR_UNSUPPORTED, "N = %u with %u digit polynomials does not fit in shared memory", N, c->rows); }
+        const uint64_t Q = p->Q;
+        std::vector<uint64_t> tw, twi, pw(2 * (size_t)N);
+        ntt_tables(N, Q, c->p.psi, tw, twi);
+        pw[0] = 1;
+        for (uint32_t i = 1; i < 2 * N; ++i) pw[i] = mulmod(pw[i - 1], c->p.psi, Q);
+        W.ninv = invmod_prime(N % Q, Q);
+        int rcw = 0;
+        if (W.wsize == 8) {
+            W.ninv_s = shoup64(W.ninv, Q);
+            W.mu = (uint64_t)((((u128_t)1) << 64) / Q);
+            W.r = (uint64_t)((((u128_t)1) << 64) % Q);
+            W.rs = shoup64(W.r, Q);
+            std::vector<ulonglong2> t(N), ti(N);
+            for (uint32_t i = 0; i < N; ++i) { t[i] = make_ulonglong2(tw[i], shoup64(tw[i], Q)); ti[i] = make_ulonglong2(twi[i], shoup64(twi[i], Q)); }
+            rcw = W.tw.ensure(N * 16); if (!rcw) rcw = W.twi.ensure(N * 16); if (!rcw) rcw = W.pw.ensure(2 * (size_t)N * 8);
+            if (!rcw && (cudaMemcpy(W.tw.p, t.data(), N * 16, cudaMemcpyHostToDevice) != cudaSuccess ||
+                         cudaMemcpy(W.twi.p, ti.data(), N * 16, cudaMemcpyHostToDevice) != cudaSuccess ||
+                         cudaMemcpy(W.pw.p, pw.data(), 2 * (size_t)N * 8, cudaMemcpyHostToDevice) != cudaSuccess))
+                rcw = lb_fail(LUXB200_ERR_CUDA, "table upload failed");
+        } else {
+            W.ninv_s = shoup32(W.ninv, Q);
+            W.mu = (uint64_t)((1ull << 32) / Q);
+            W.r = (uint64_t)((1ull << 32) % Q);
+            W.rs = shoup32(W.r, Q);
+            std::vector<uint2> t(N), ti(N);
+            std::vector<u32> pw32(2 * (size_t)N);
+            for (uint32_t i = 0; i < N; ++i) { t[i] = make_uint2((u32)tw[i], shoup32(tw[i], Q)); ti[i] = make_uint2((u32)twi[i], shoup32(twi[i], Q)); }
+            for (uint32_t i = 0; i < 2 * N; ++i) pw32[i] = (u32)pw[i];
+            rcw = W.tw.ensure(N * 8); if (!rcw) rcw = W.twi.ensure(N * 8); if (!rcw) rcw = W.pw.ensure(2 * (size_t)N * 4);
+            if (!rcw && (cudaMemcpy(W.tw.p, t.data(), N * 8, cudaMemcpyHostToDevice) != cudaSuccess ||
+                         cudaMemcpy(W.twi.p, ti.data(), N * 8, cudaMemcpyHostToDevice) != cudaSuccess ||
+                         cudaMemcpy(W.pw.p, pw32.data(), 2 * (size_t)N * 4, cudaMemcpyHostToDevice) != cudaSuccess))
+                rcw = lb_fail(LUXB200_ERR_CUDA, "table upload failed");
+        }
+        if (rcw) { luxb200_ctx_destroy(c); return rcw; }
+    }
+    int rc = 0;
+    if (!c->wide.on) {
     // reduce64 constants: x < max(rows * 2Q * Q, 8 Q^2 + 4Q)
     {
         u128_t Q = p->Q, xmax = (u128_t)c->rows * 2 * Q * Q;
@@ -129,12 +180,13 @@ int luxb200_ctx_create(const luxb200_params* p, int device, luxb200_ctx** out) {
         c->red_s = s;
         c->red_mu = (uint32_t)((((u128_t)1) << (s + 32)) / Q);
     }
-    int rc = c->ntt.build(p->N, p->Q, c->p.psi);
+    rc = c->ntt.build(p->N, p->Q, c->p.psi);
+    }
     if (rc) { luxb200_ctx_destroy(c); return rc; }
     cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
     for (int i = 0; i < 5 && e == cudaSuccess; ++i) e = cudaEventCreate(&c->ev[i]);
     if (e != cudaSuccess) { luxb200_ctx_destroy(c); return lb_fail(LUXB200_ERR_CUDA, "stream/event creation failed: %s", cudaGetErrorString(e)); }
-    if (p->method == LUXB200_GINX) {
+    if (p->method == LUXB200_GINX && !c->wide.on) {
         // monomials X^a - 1 in EVALUATION format (rgsw-cryptoparameters.cpp:96-113), sigma order:
         // value at index p is psi^(a (2 brv(p) + 1)) - 1
         const uint32_t N = p->N, M = 2 * N, E = N / 32;
@@ -170,8 +222,18 @@ int luxb200_ctx_create(const luxb200_params* p, int device, luxb200_ctx** out) {
                 h[(size_t)t * N + (rd >> 2) * 128 + 4 * ld + (rd & 3)] = src;  // natural EVAL index of the source
             }
         }
-        rc = c->automap.ensure(h.size() * 4);
-        if (!rc && cudaMemcpy(c->automap.p, h.data(), h.size() * 4, cudaMemcpyHostToDevice) != cudaSuccess)
+        if (c->wide.on) {   // natural order for the shared-memory kernel: out[brv(j)] = in[brv(idx)]
+            for (uint32_t t = 0; t <= w; ++t) {
+                uint32_t k = (t == 0) ? M - 5 : (uint32_t)powmod(5, t, M);
+                for (uint32_t j = 0; j < N; ++j) {
+                    uint32_t idx = (uint32_t)(((uint64_t)(2 * j + 1) * k) % M) >> 1;
+                    h[(size_t)t * N + bitrev(j, c->logN)] = bitrev(idx, c->logN);
+                }
+            }
+        }
+        DevBuf& amap = c->wide.on ? c->wide.automap : c->automap;
+        rc = amap.ensure(h.size() * 4);
+        if (!rc && cudaMemcpy(amap.p, h.data(), h.size() * 4, cudaMemcpyHostToDevice) != cudaSuccess)
             rc = lb_fail(LUXB200_ERR_CUDA, "automap upload failed");
         if (rc) { luxb200_ctx_destroy(c); return rc; }
         // logGen (rgsw-cryptoparameters.cpp:115-127)
@@ -189,7 +251,7 @@ int luxb200_ctx_create(const luxb200_params* p, int device, luxb200_ctx** out) {
         if (rc) { luxb200_ctx_destroy(c); return rc; }
     }
     // KSK element type
-    c->ks_elem = (p->qKS <= 65536) ? 2 : 4;
+    c->ks_elem = (p->qKS <= 65536) ? 2 : (p->qKS <= (1ull << 32)) ? 4 : 8;
     c->npad = (p->n + 7) & ~7u;
     *out = c;
     return 0;
@@ -203,6 +265,7 @@ void luxb200_ctx_destroy(luxb200_ctx* c) {
                       &c->tmpc, &c->tmpd, &c->cpa, &c->cpb, &c->cdesc, &c->clsel, &c->cx1a, &c->cx1b, &c->cx2a, &c->cx2b,
                       &c->xin};
     for (DevBuf* b : bufs) b->release();
+    c->wide.tw.release(); c->wide.twi.release(); c->wide.pw.release(); c->wide.automap.release();
     c->ntt.release();
     for (int s = 0; s < 2; ++s) {
         for (DevBuf& b : c->pipe.in[s]) b.release();
@@ -244,6 +307,14 @@ int luxb200_load_bsk(luxb200_ctx* c, const uint64_t* bsk, int on_device) {
     LB_LOCK(c);
     LB_TRY(lb_set_device(c->device));
     const uint64_t len = luxb200_bsk_len(c);
+    if (c->wide.on && c->wide.wsize == 8) {
+        // 64-bit residues in natural EVALUATION order: the canonical layout IS the device layout
+        LB_TRY(c->bsk.ensure(len * 8));
+        LB_CUDA(cudaMemcpyAsync(c->bsk.p, bsk, len * 8, on_device ? cudaMemcpyDeviceToDevice : cudaMemcpyHostToDevice, c->stream));
+        LB_CUDA(cudaStreamSynchronize(c->stream));
+        c->have_bsk = true;
+        return 0;
+    }
     LB_TRY(c->bsk.ensure(len * 4));
     // stream the canonical u64 key through a bounded staging buffer
     const uint64_t chunk = (uint64_t)c->p.N * 4096;  // polynomials are N-aligned
@@ -256,7 +327,8 @@ int luxb200_load_bsk(luxb200_ctx* c, const uint64_t* bsk, int on_device) {
             LB_CUDA(cudaMemcpyAsync(stage.p, bsk + off, m * 8, cudaMemcpyHostToDevice, c->stream));
             src = stage.as<u64>();
         }
-        pack_polys_sigma_kernel<<<nblk(m, 256), 256, 0, c->stream>>>(src, c->bsk.as<u32>() + off, c->logN, m);
+        if (c->wide.on) narrow_u64_u32_kernel<<<nblk(m, 256), 256, 0, c->stream>>>(src, c->bsk.as<u32>() + off, m);
+        else pack_polys_sigma_kernel<<<nblk(m, 256), 256, 0, c->stream>>>(src, c->bsk.as<u32>() + off, c->logN, m);
         c->launches++;
     }
     LB_CUDA(cudaStreamSynchronize(c->stream));
@@ -271,7 +343,7 @@ int luxb200_load_ksk(luxb200_ctx* c, const uint64_t* A, const uint64_t* B, int o
     LB_TRY(lb_set_device(c->device));
     const uint64_t rows = (uint64_t)c->p.N * c->p.baseKS * c->digitsKS;
     LB_TRY(c->kskA.ensure(rows * c->npad * c->ks_elem));
-    LB_TRY(c->kskB.ensure(rows * 4));
+    LB_TRY(c->kskB.ensure(rows * (c->ks_elem == 8 ? 8 : 4)));
     const uint64_t chunk_rows = 65536;
     DevBuf stage;
     if (!on_device) LB_TRY(stage.ensure(std::min(rows, chunk_rows) * c->p.n * 8));
@@ -285,8 +357,11 @@ int luxb200_load_ksk(luxb200_ctx* c, const uint64_t* A, const uint64_t* B, int o
         if (c->ks_elem == 2)
             pack_ksk_kernel<uint16_t><<<nblk(m * c->npad, 256), 256, 0, c->stream>>>(
                 src, c->kskA.as<uint16_t>() + r0 * c->npad, c->p.n, c->npad, m);
-        else
+        else if (c->ks_elem == 4)
             pack_ksk_kernel<u32><<<nblk(m * c->npad, 256), 256, 0, c->stream>>>(src, c->kskA.as<u32>() + r0 * c->npad,
+                                                                               c->p.n, c->npad, m);
+        else
+            pack_ksk_kernel<u64><<<nblk(m * c->npad, 256), 256, 0, c->stream>>>(src, c->kskA.as<u64>() + r0 * c->npad,
                                                                                c->p.n, c->npad, m);
         c->launches++;
     }
@@ -298,7 +373,8 @@ int luxb200_load_ksk(luxb200_ctx* c, const uint64_t* A, const uint64_t* B, int o
             LB_CUDA(cudaMemcpyAsync(sb.p, B, rows * 8, cudaMemcpyHostToDevice, c->stream));
             src = sb.as<u64>();
         }
-        narrow_u64_u32_kernel<<<nblk(rows, 256), 256, 0, c->stream>>>(src, c->kskB.as<u32>(), rows);
+        if (c->ks_elem == 8) copy_u64_kernel<<<nblk(rows, 256), 256, 0, c->stream>>>(src, c->kskB.as<u64>(), rows);
+        else narrow_u64_u32_kernel<<<nblk(rows, 256), 256, 0, c->stream>>>(src, c->kskB.as<u32>(), rows);
         c->launches++;
         LB_CUDA(cudaStreamSynchronize(c->stream));
         sb.release();
@@ -356,9 +432,9 @@ int luxb200_broadcast_keys(luxb200_ctx* const* ctxs, int n) {
             if (ctxs[j] == c) return lb_fail(LUXB200_ERR_INVALID_ARG, "luxb200_broadcast_keys: context %d listed twice", i);
     }
     // whichever of the two keys the root holds is sent (a backend may bind a refresh key before a switching key exists)
-    const size_t bsk_bytes = r->have_bsk ? luxb200_bsk_len(r) * 4 : 0;
+    const size_t bsk_bytes = r->have_bsk ? luxb200_bsk_len(r) * ((r->wide.on && r->wide.wsize == 8) ? 8 : 4) : 0;
     const size_t rowsK = (size_t)r->p.N * r->p.baseKS * r->digitsKS;
-    const size_t ka_bytes = r->have_ksk ? rowsK * r->npad * r->ks_elem : 0, kb_bytes = r->have_ksk ? rowsK * 4 : 0;
+    const size_t ka_bytes = r->have_ksk ? rowsK * r->npad * r->ks_elem : 0, kb_bytes = r->have_ksk ? rowsK * (r->ks_elem == 8 ? 8 : 4) : 0;
     for (int i = 1; i < n; ++i) {
         luxb200_ctx* c = ctxs[i];
         LB_TRY(lb_set_device(c->device));

@@ -86,6 +86,14 @@ struct luxb200_ctx {
     cudaStream_t stream = nullptr;
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     Ntt32Tables ntt;
+    // "wide" contexts (br_wide.cuh): N = 2048, 64-bit Q, or a digit count the register-resident kernels are not built for
+    struct Wide {
+        bool on = false;
+        uint32_t wsize = 4;                    // bytes per residue on the device: 4 (Q < 2^30) or 8
+        DevBuf tw, twi, pw, automap;           // (w, Shoup) tables [N] x 2, psi powers [2N], natural-order automorphism maps
+        uint64_t ninv = 0, ninv_s = 0, mu = 0, r = 0, rs = 0;
+        size_t smem = 0;                       // dynamic shared memory of brw_kernel
+    } wide;
     DevBuf bsk, mono, kskA, kskB, automap, loggen;
     bool have_bsk = false, have_ksk = false;
     // work buffers
@@ -113,8 +121,8 @@ int lb_set_device(int device);
 
 // ---- entry points of api.cu used by circuit.cu (a separate translation unit, same library) -------------------
 // test-vector table of a 2-input gate for plaintext modulus p (binfhe-base-scheme.cpp:535-567)
-void lb_gate_lut(const luxb200_ctx* c, int gate, uint64_t p, std::vector<uint32_t>& lut);
-int lb_upload_lut(luxb200_ctx* c, const std::vector<uint32_t>& lut);
+void lb_gate_lut(const luxb200_ctx* c, int gate, uint64_t p, std::vector<uint64_t>& lut);
+int lb_upload_lut(luxb200_ctx* c, const std::vector<uint64_t>& lut);
 // blind rotation + extraction + SwitchCTtoqn on prepared device inputs; lutsel: optional per-item offsets into c->lut
 int lb_boot_dev(luxb200_ctx* c, const uint32_t* d_a, const uint32_t* d_b, uint64_t ctmod, uint64_t b_add, uint64_t fmod,
                 uint32_t* d_oa, uint32_t* d_ob, uint64_t count, const uint32_t* lutsel);

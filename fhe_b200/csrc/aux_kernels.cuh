@@ -35,6 +35,10 @@ __global__ void narrow_u64_u32_kernel(const u64* __restrict__ in, u32* __restric
     const u64 idx = (u64)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx < total) out[idx] = (u32)in[idx];
 }
+__global__ void copy_u64_kernel(const u64* __restrict__ in, u64* __restrict__ out, u64 total) {
+    const u64 idx = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx < total) out[idx] = in[idx];
+}
 __global__ void widen_u32_u64_kernel(const u32* __restrict__ in, u64* __restrict__ out, u64 total) {
     const u64 idx = (u64)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx < total) out[idx] = in[idx];
@@ -89,23 +93,27 @@ __global__ void modswitch_kernel(const u64* __restrict__ in, u64* __restrict__ o
 
 // ---- SwitchCTtoqn (lwe-pke.cpp:170-178): ModSwitch(Q->qKS) + KeySwitch (lwe-pke.cpp:348-372) + ModSwitch(qKS->fmod)
 struct KsParams {
-    const u32* in;      // [count][N+1]  (a then b), mod Qin
+    const void* in;     // IN [count][N+1]  (a then b), mod Qin
     const void* kA;     // KT [N*baseKS*digits][npad]
-    const u32* kB;      // [N*baseKS*digits]
-    u32* out_a;         // [count][out_stride] first n entries
-    u32* out_b;         // [count]
+    const u32* kB32;    // [N*baseKS*digits]  (qKS <= 2^32)
+    const u64* kB64;    //                    (qKS >  2^32)
+    void* out_a;        // [count][out_stride] first n entries; u32, or u64 when out64
+    void* out_b;        // [count]
     u64 Qin, qKS, fmod;
     u32 N, n, npad, baseKS, digits, out_stride;
     u32 ms_in, ms_out;  // apply RoundqQ on input (Qin->qKS) / output (qKS->fmod)
+    u32 out64, pad;
     u64 count;
 };
 
-template <typename KT, typename ACC>
+// KT: key element (u16 / u32 / u64 by the size of qKS), ACC: column accumulator (N * digits * qKS must fit),
+// IN: residue type of the extracted ciphertexts (u32, or u64 for the 64-bit blind rotation)
+template <typename KT, typename ACC, typename IN>
 __global__ void __launch_bounds__(128) keyswitch_kernel(const KsParams P) {
     extern __shared__ u32 rowidx[];  // [N*digits]
     __shared__ u64 bred[128];
     const u64 ct = blockIdx.x;
-    const u32* in = P.in + ct * (P.N + 1);
+    const IN* in = reinterpret_cast<const IN*>(P.in) + ct * (P.N + 1);
     const u32 R = P.N * P.digits;
     for (u32 i = threadIdx.x; i < P.N; i += blockDim.x) {
         u64 v = in[i];
@@ -119,9 +127,12 @@ __global__ void __launch_bounds__(128) keyswitch_kernel(const KsParams P) {
     __syncthreads();
     constexpr int VEC = 8 / sizeof(KT);
     const KT* kA = reinterpret_cast<const KT*>(P.kA);
-    // b: each thread sums a strided subset of the B entries
+    // b: each thread sums a strided subset of the B entries (modular: the entries may be up to 2^62)
     u64 bs = 0;
-    for (u32 r = threadIdx.x; r < R; r += blockDim.x) bs += P.kB[rowidx[r]];
+    for (u32 r = threadIdx.x; r < R; r += blockDim.x) {
+        bs += P.kB64 ? P.kB64[rowidx[r]] : (u64)P.kB32[rowidx[r]];
+        if (bs >= P.qKS) bs %= P.qKS;
+    }
     bred[threadIdx.x] = bs;
     for (u32 k0 = threadIdx.x * VEC; k0 < P.npad; k0 += blockDim.x * VEC) {
         ACC acc[VEC];
@@ -137,12 +148,14 @@ __global__ void __launch_bounds__(128) keyswitch_kernel(const KsParams P) {
             for (int u = 0; u < 8; ++u) {
                 if (VEC == 4) {
                     acc[0] += v[u].x & 0xffffu;
-                    acc[1] += v[u].x >> 16;
+                    acc[1 % VEC] += v[u].x >> 16;
                     acc[2 % VEC] += v[u].y & 0xffffu;
                     acc[3 % VEC] += v[u].y >> 16;
-                } else {
+                } else if (VEC == 2) {
                     acc[0] += v[u].x;
-                    acc[1] += v[u].y;
+                    acc[1 % VEC] += v[u].y;
+                } else {
+                    acc[0] += (ACC)((u64)v[u].x | ((u64)v[u].y << 32));
                 }
             }
         }
@@ -150,12 +163,14 @@ __global__ void __launch_bounds__(128) keyswitch_kernel(const KsParams P) {
             const uint2 v = __ldg(reinterpret_cast<const uint2*>(kA + (size_t)rowidx[r] * P.npad + k0));
             if (VEC == 4) {
                 acc[0] += v.x & 0xffffu;
-                acc[1] += v.x >> 16;
+                acc[1 % VEC] += v.x >> 16;
                 acc[2 % VEC] += v.y & 0xffffu;
                 acc[3 % VEC] += v.y >> 16;
-            } else {
+            } else if (VEC == 2) {
                 acc[0] += v.x;
-                acc[1] += v.y;
+                acc[1 % VEC] += v.y;
+            } else {
+                acc[0] += (ACC)((u64)v.x | ((u64)v.y << 32));
             }
         }
 #pragma unroll
@@ -165,20 +180,22 @@ __global__ void __launch_bounds__(128) keyswitch_kernel(const KsParams P) {
                 u64 s = (u64)acc[e] % P.qKS;
                 u64 v = s ? P.qKS - s : 0;  // a = 0 - sum
                 if (P.ms_out) v = round_qQ(v, P.fmod, P.qKS);
-                P.out_a[ct * P.out_stride + k] = (u32)v;
+                if (P.out64) reinterpret_cast<u64*>(P.out_a)[ct * P.out_stride + k] = v;
+                else reinterpret_cast<u32*>(P.out_a)[ct * P.out_stride + k] = (u32)v;
             }
         }
     }
     __syncthreads();
     if (threadIdx.x == 0) {
         u64 s = 0;
-        for (int i = 0; i < 128; ++i) s += bred[i];
+        for (int i = 0; i < 128; ++i) { s += bred[i]; if (s >= P.qKS) s %= P.qKS; }
         s %= P.qKS;
         u64 b = in[P.N];
         if (P.ms_in) b = round_qQ(b, P.qKS, P.Qin);
         b = (b + P.qKS - s) % P.qKS;
         if (P.ms_out) b = round_qQ(b, P.fmod, P.qKS);
-        P.out_b[ct] = (u32)b;
+        if (P.out64) reinterpret_cast<u64*>(P.out_b)[ct] = b;
+        else reinterpret_cast<u32*>(P.out_b)[ct] = (u32)b;
     }
 }
 

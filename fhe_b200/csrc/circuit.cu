@@ -191,7 +191,7 @@ extern "C" int luxb200_circuit_batch(luxb200_ctx* c, uint32_t n_inputs, const lu
         LB_CUDA(cudaGetLastError());
     }
     if (n_boot) {
-        std::vector<u32> luts, one;
+        std::vector<uint64_t> luts, one;
         for (int g = LUXB200_OR; g <= LUXB200_XNOR; ++g) {
             lb_gate_lut(c, g, 4, one);
             luts.insert(luts.end(), one.begin(), one.end());

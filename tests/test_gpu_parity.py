@@ -447,3 +447,96 @@ def test_evalfunc_lmkcdey_decrypt_failures_are_the_references():
                                  os.cpu_count() or 8) == 0
     assert (oa[sel] == xa).all() and (ob[sel] == xb).all()
     ctx.close(); oc.close()
+
+
+# ---- the "wide" contexts: N = 2048, Q above 2^30 (64-bit residues), 1 / 4 / 5 gadget digits (csrc/br_wide.cuh) ------------------
+@pytest.mark.parametrize("name,method,cnt", [("STD256", "GINX", 3),              # 29-bit Q, N = 2048, 2 digits
+                                             ("STD256_3", "GINX", 2),            # 3 digits
+                                             ("STD256Q_3", "GINX", 2),           # 27-bit Q, baseG = 64: 4 digits
+                                             ("STD192", "GINX", 2),              # 37-bit Q: 64-bit residues, 1 digit
+                                             ("STD192Q_3", "GINX", 2),           # 34-bit Q, 2 digits, baseKS = 16
+                                             ("STD128Q_3", "GINX", 2),           # 50-bit Q
+                                             ("STD192_LMKCDEY", "LMKCDEY", 2),   # 39-bit Q, Gaussian key
+                                             ("STD256_LMKCDEY", "LMKCDEY", 2),   # 30-bit Q (4Q just below 2^32)
+                                             ("STD256Q_4_LMKCDEY", "LMKCDEY", 2),  # qKS = 2^17, 4 digits
+                                             ("STD192Q_LMKCDEY", "LMKCDEY", 2)])
+def test_wide_sets_vs_oracle(name, method, cnt):
+    """every N = 2048 row family of binfhecontext.cpp:121-158 against the oracle on seeded keys: gates (both output
+    formats) and Bootstrap"""
+    from fhe_b200.context import BinFHEContext
+    ctx = BinFHEContext().GenerateBinFHEContext(name, method)
+    oc = oracle_twin(ctx, method)
+    sk, bsk, A, B = oc.keygen(seed=7, key_dist=getattr(ctx, "keyDist", 0))
+    ctx.BTKeyLoad(bsk, A, B)
+    a1, b1 = _seeded_inputs(oc, sk, cnt, 0)
+    a2, b2 = _seeded_inputs(oc, sk, cnt, 1)
+    a1[0, : ctx.n // 2] = 0
+    thr = os.cpu_count() or 8
+    for g, ext in (("NAND", False), ("XOR", True)):
+        (oa, ob), res = ctx.EvalBinGateBatch(g, (a1, b1), (a2, b2), ext)
+        assert res.success, res.error
+        xa, xb = oc.evalbingate(g, a1, b1, a2, b2, ext, threads=thr)
+        assert (oa == xa).all() and (ob == xb).all(), (name, method, g, ext)
+    (oa, ob), res = ctx.BootstrapBatch((a2, b2))
+    assert res.success, res.error
+    xa = np.zeros((cnt, ctx.n), np.uint64); xb = np.zeros(cnt, np.uint64)
+    oracle().orc_bootstrap(oc.h, P(a2), P(b2), P(xa), P(xb), cnt, 4, 0, thr)
+    assert (oa == xa).all() and (ob == xb).all()
+    assert [oc.decrypt(sk, oa[i], ob[i]) for i in range(cnt)] == [(i >> 1) & 1 for i in range(cnt)]
+    ctx.close(); oc.close()
+
+
+@pytest.mark.parametrize("method", ["GINX", "AP", "LMKCDEY"])
+@pytest.mark.parametrize("bits,N,baseG,qKS", [(54, 2048, 1 << 14, 1 << 35),    # the large-precision shape: 3 digits, u64 key-switch key
+                                              (54, 2048, 1 << 27, 1 << 35),    # 1 digit
+                                              (27, 1024, 1 << 5, 1 << 14),     # logQ = 11 context: 5 digits at N = 1024
+                                              (27, 1024, 1 << 14, 1 << 14),    # 1 digit at N = 1024
+                                              (45, 512, 1 << 15, 1 << 20)])    # small ring, 64-bit residues
+def test_wide_custom_params_all_methods(method, bits, N, baseG, qKS):
+    """hand-made parameter sets with a short LWE key (n = 24) so that AP (whose key grows with baseR * digitsR) is cheap:
+    all three methods through the shared-memory kernel, every primitive of the path against the oracle — gates, EvalFunc,
+    raw EvalAcc (BlindRotateBatch), ExternalProductBatch, KeySwitchBatch with 64-bit residues."""
+    from fhe_b200.context import BinFHEContext
+    O = oracle()
+    ctx = BinFHEContext()
+    Q = ctx.L.luxb200_last_prime(bits, 2 * N)
+    ctx.GenerateFromParams(n=24, N=N, q=2 * N if method == "LMKCDEY" else N, Q=Q, qKS=qKS, baseKS=32, baseG=baseG, baseR=8,
+                           numAutoKeys=6, method=method)
+    oc = oracle_twin(ctx, method)
+    sk, bsk, A, B = oc.keygen(seed=11)
+    ctx.BTKeyLoad(bsk, A, B)
+    cnt = 5
+    a1, b1 = _seeded_inputs(oc, sk, cnt, 0)
+    a2, b2 = _seeded_inputs(oc, sk, cnt, 1)
+    for g, ext in (("AND", False), ("XNOR", True), ("OR", False)):
+        (oa, ob), res = ctx.EvalBinGateBatch(g, (a1, b1), (a2, b2), ext)
+        assert res.success, res.error
+        xa, xb = oc.evalbingate(g, a1, b1, a2, b2, ext)
+        assert (oa == xa).all() and (ob == xb).all(), (method, g, ext)
+    # EvalFunc: negacyclic and periodic (and arbitrary when q <= N)
+    p = 4
+    for f in (lambda x, pp: x + 1 if x < pp // 2 else pp - (x - pp // 2 + 1), lambda x, pp: x % (pp // 2), lambda x, pp: (3 * x + 1) % pp):
+        lut = ctx.GenerateLUTviaFunction(f, p)
+        (oa, ob), res = ctx.EvalFuncBatch((a1, b1), lut)
+        lut64 = np.ascontiguousarray(lut, np.uint64)
+        xa = np.zeros((cnt, ctx.n), np.uint64); xb = np.zeros(cnt, np.uint64)
+        rc = O.orc_evalfunc(oc.h, P(a1), P(b1), P(lut64), len(lut64), ctx.GetBeta(), P(xa), P(xb), cnt, ctx.q, 8)
+        assert res.success == (rc == 0)
+        if rc == 0:
+            assert (oa == xa).all() and (ob == xb).all()
+    # raw EvalAcc on random accumulators
+    rng = np.random.default_rng(bits + N)
+    acc = rng.integers(0, Q, size=(2, 2, N), dtype=np.uint64)
+    got = ctx.BlindRotateBatch(a1[:2], acc)
+    for i in range(2):
+        ref = acc[i].copy()
+        O.orc_evalacc(oc.h, P(np.ascontiguousarray(a1[i])), ctx.q, P(ref))
+        assert (got[i] == ref).all()
+    # KeySwitch on (N, qKS) inputs — 64-bit residues when qKS is above 2^32
+    ka = rng.integers(0, qKS, size=(3, N), dtype=np.uint64); kb = rng.integers(0, qKS, size=3, dtype=np.uint64)
+    oa, ob = ctx.KeySwitchBatch((ka, kb))
+    for i in range(3):
+        xa = np.zeros(ctx.n, np.uint64); xb = np.zeros(1, np.uint64)
+        O.orc_keyswitch(oc.h, P(np.ascontiguousarray(ka[i])), int(kb[i]), P(xa), P(xb))
+        assert (oa[i] == xa).all() and ob[i] == xb[0]
+    ctx.close(); oc.close()

@@ -84,3 +84,34 @@ def test_dcrt_switchformat_is_per_limb_ntt():
         assert (a == b).all()
         assert R.ref_dcrt_switchformat(N, L, bits, P(a), cnt, 1) == 0
         assert (a == x).all()
+
+
+@pytest.mark.parametrize("method", ["GINX", "AP", "LMKCDEY"])
+@pytest.mark.parametrize("bits,cyc,baseG", [(54, 4096, 1 << 14), (37, 4096, 1 << 19), (29, 4096, 64), (27, 2048, 32)])
+def test_wide_regime_pins_the_oracle(method, bits, cyc, baseG):
+    """The regimes the shared-memory GPU kernel serves — N = 2048, Q up to 54 bits, 1 to 5 gadget digits — pinned on the
+    CPU: the real reference with a hand-made parameter set (short LWE key, so it runs in seconds) against the oracle on
+    the reference's own keys: gates in both output formats and Bootstrap."""
+    R, O = orclib.ref(), orclib.oracle()
+    N = cyc // 2
+    q = 2 * N if method == "LMKCDEY" else N
+    rc = RefContext(None, method, custom=(bits, cyc, 12, q, 1 << 20, 32, baseG, 8, 6, 0))
+    rc.keygen()
+    oc = OrcContext(rc.p)
+    assert (oc.p.digitsG, oc.p.digitsKS, oc.p.psi, oc.p.Q) == (rc.p.digitsG, rc.p.digitsKS, rc.p.psi, rc.p.Q)
+    oc.load(rc.dump_bsk(), *rc.dump_ksk())
+    p, cnt = rc.p, 3
+    a1 = np.zeros((cnt, p.n), np.uint64); b1 = np.zeros(cnt, np.uint64); a2 = a1.copy(); b2 = b1.copy()
+    for i in range(cnt):
+        a1[i], b1[i] = rc.encrypt(i & 1); a2[i], b2[i] = rc.encrypt((i >> 1) & 1)
+    for g in ("NAND", "XOR"):
+        for ext in (0, 1):
+            oa = np.zeros((cnt, p.N if ext else p.n), np.uint64); ob = np.zeros(cnt, np.uint64)
+            assert R.ref_evalbingate(rc.h, GATE[g], P(a1), P(b1), P(a2), P(b2), P(oa), P(ob), cnt, ext, 4) == 0
+            xa, xb = oc.evalbingate(g, a1, b1, a2, b2, bool(ext), threads=4)
+            assert (oa == xa).all() and (ob == xb).all(), (method, g, ext)
+    oa = np.zeros((cnt, p.n), np.uint64); ob = np.zeros(cnt, np.uint64); xa = oa.copy(); xb = ob.copy()
+    R.ref_bootstrap(rc.h, P(a1), P(b1), P(oa), P(ob), cnt, 4, 0, 4)
+    O.orc_bootstrap(oc.h, P(a1), P(b1), P(xa), P(xb), cnt, 4, 0, 4)
+    assert (oa == xa).all() and (ob == xb).all()
+    rc.close(); oc.close()
