@@ -213,6 +213,17 @@ class BinFHEContext:
             out[i] = v
         return out
 
+    # -- large precision (binfhe-base-scheme.cpp:335-521) -------------------------------------------------
+    def EvalFloorBatch(self, ct, mod, roundbits=0):
+        """BinFHEContext::EvalFloor (binfhecontext.cpp:346-357) per element; ct = (a [count][n], b [count]) mod `mod`."""
+        a, b = map(self._u64, ct)
+        cnt = len(b)
+        oa = np.empty((cnt, self.n), np.uint64)
+        ob = np.empty(cnt, np.uint64)
+        rc = self.L.luxb200_evalfloor_batch(self.h, _l.ptr(a), _l.ptr(b), _l.ptr(oa), _l.ptr(ob), cnt, mod, self.GetBeta(),
+                                            roundbits)
+        return (oa, ob), self._result(rc, cnt)
+
     # -- device-resident operators (uint32 tensors already in HBM; pointers as ints) ------------------------
     # -- gate circuits (BatchDAG, binfhe-batch.h:255-279) ------------------------------------------------
     def EvalCircuitBatch(self, n_inputs, gates, outputs, in_a, in_b):
@@ -303,3 +314,72 @@ class NTTPlan:
         if self.h:
             self.L.luxb200_ntt_plan_destroy(self.h)
             self.h = None
+
+
+# ---- large-precision contexts: GenerateBinFHEContext(set, arbFunc, logQ, N, GINX, timeOptimization) ------------------
+def GenerateLargePrecisionContexts(paramset, arbFunc=False, logQ=11, N=0, timeOptimization=False, device=0):
+    """binfhecontext.cpp:53-104: Q = LastPrime(54, 2N) (27 bits for logQ = 11), N = max(N, FindRingDim(ternary, 128 classic,
+    logQ')) — 2048 for 54 bits, 1024 for 27 (stdlatticeparms.cpp:169-172) — q = N (arbFunc) or 2N, qKS = 2^35, baseKS = 32,
+    n = 32 (TOY) or 1305 (STD128), baseR = 23, GINX.  Returns the list of device contexts, the current gadget base first;
+    with timeOptimization (and logQ != 11) one per base of the reference's key map (2^14, 2^18, 2^27,
+    rgsw-cryptoparameters.cpp:49-66), as BTKeyGen fills it (binfhecontext.cpp:292-298)."""
+    if paramset not in ("TOY", "STD128"):
+        raise _l.LuxB200Error(-1, "STD128 and TOY are the only supported sets")
+    if logQ > 29 or logQ < 11:
+        raise _l.LuxB200Error(-1, "logQ must be in [11, 29]")
+    logQp = 54
+    if logQ > 25:
+        baseG = 1 << 14
+    elif logQ > 16:
+        baseG = 1 << 18
+    elif logQ > 11:
+        baseG = 1 << 27
+    else:
+        baseG, logQp = 1 << 5, 27
+    ring = max(N, 2048 if logQp == 54 else 1024)
+    L = _l.load()
+    Q = L.luxb200_last_prime(logQp, 2 * ring)
+    q = ring if arbFunc else 2 * ring
+    n = 32 if paramset == "TOY" else 1305
+    bases = [baseG]
+    if timeOptimization and logQ != 11:
+        bases += [b for b in (1 << 14, 1 << 18, 1 << 27) if b != baseG]
+    out = []
+    for bg in bases:
+        c = BinFHEContext(device=device)
+        c.GenerateFromParams(n=n, N=ring, q=q, Q=Q, qKS=1 << 35, baseKS=32, baseG=bg, baseR=23, numAutoKeys=10, method="GINX")
+        c.keyDist = 0
+        out.append(c)
+    return out
+
+
+def _ctx_array(ctxs):
+    return (C.c_void_p * len(ctxs))(*[c.h for c in ctxs])
+
+
+def EvalSignBatch(ctxs, ct, mod, schemeSwitch=False):
+    """BinFHEContext::EvalSign (binfhecontext.cpp:359-364) per element over the key map `ctxs` (current base first; three
+    contexts = the reference's dynamic mode).  Returns ((a, b) mod q, BatchResult)."""
+    c0 = ctxs[0]
+    a, b = map(c0._u64, ct)
+    cnt = len(b)
+    oa = np.empty((cnt, c0.n), np.uint64)
+    ob = np.empty(cnt, np.uint64)
+    rc = c0.L.luxb200_evalsign_batch(_ctx_array(ctxs), len(ctxs), _l.ptr(a), _l.ptr(b), _l.ptr(oa), _l.ptr(ob), cnt, mod,
+                                     c0.GetBeta(), int(schemeSwitch))
+    return (oa, ob), c0._result(rc, cnt)
+
+
+def EvalDecompBatch(ctxs, ct, mod):
+    """BinFHEContext::EvalDecomp (binfhecontext.cpp:366-370): ((a [k][count][n], b [k][count], moduli [k]), BatchResult)."""
+    c0 = ctxs[0]
+    a, b = map(c0._u64, ct)
+    cnt = len(b)
+    k = int(c0.L.luxb200_evaldecomp_count(c0.q, mod, c0.GetBeta()))
+    oa = np.empty((k, cnt, c0.n), np.uint64)
+    ob = np.empty((k, cnt), np.uint64)
+    om = np.zeros(k, np.uint64)
+    nout = C.c_uint32(0)
+    rc = c0.L.luxb200_evaldecomp_batch(_ctx_array(ctxs), len(ctxs), _l.ptr(a), _l.ptr(b), _l.ptr(oa), _l.ptr(ob), _l.ptr(om), k,
+                                       C.byref(nout), cnt, mod, c0.GetBeta())
+    return (oa, ob, om), c0._result(rc, cnt)

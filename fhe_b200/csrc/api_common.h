@@ -34,29 +34,30 @@ int lb_fail(int code, const char* fmt, ...);
 struct DevBuf {
     void* p = nullptr;
     size_t cap = 0;
+    bool borrowed = false;   // alias of another buffer's allocation (luxb200_share_ksk): never freed here
     DevBuf() = default;
     DevBuf(const DevBuf&) = delete;
     DevBuf& operator=(const DevBuf&) = delete;
-    DevBuf(DevBuf&& o) noexcept : p(o.p), cap(o.cap) { o.p = nullptr; o.cap = 0; }
+    DevBuf(DevBuf&& o) noexcept : p(o.p), cap(o.cap), borrowed(o.borrowed) { o.p = nullptr; o.cap = 0; o.borrowed = false; }
     DevBuf& operator=(DevBuf&& o) noexcept {
-        if (this != &o) { release(); p = o.p; cap = o.cap; o.p = nullptr; o.cap = 0; }
+        if (this != &o) { release(); p = o.p; cap = o.cap; borrowed = o.borrowed; o.p = nullptr; o.cap = 0; o.borrowed = false; }
         return *this;
     }
+    void borrow(const DevBuf& o) { release(); p = o.p; cap = o.cap; borrowed = true; }
     ~DevBuf() { release(); }
     int ensure(size_t bytes) {
         if (bytes <= cap) return 0;
-        if (p) cudaFree(p);
-        p = nullptr;
-        cap = 0;
+        release();
         cudaError_t e = cudaMalloc(&p, bytes);
         if (e != cudaSuccess) return lb_fail(LUXB200_ERR_ALLOC, "cudaMalloc(%zu) failed: %s", bytes, cudaGetErrorString(e));
         cap = bytes;
         return 0;
     }
     void release() {
-        if (p) cudaFree(p);
+        if (p && !borrowed) cudaFree(p);
         p = nullptr;
         cap = 0;
+        borrowed = false;
     }
     template <typename T>
     T* as() { return reinterpret_cast<T*>(p); }

@@ -50,6 +50,11 @@ SIGNATURES = {
     "luxb200_broadcast_keys": (INT, [VP, INT]),
     "luxb200_host_alloc": (INT, [U64, C.POINTER(VP)]),
     "luxb200_host_free": (INT, [VP]),
+    "luxb200_evalfloor_batch": (INT, [VP, VP, VP, VP, VP, U64, U64, U64, U32]),
+    "luxb200_evalsign_batch": (INT, [VP, INT, VP, VP, VP, VP, U64, U64, U64, INT]),
+    "luxb200_evaldecomp_batch": (INT, [VP, INT, VP, VP, VP, VP, VP, U32, VP, U64, U64, U64]),
+    "luxb200_evaldecomp_count": (U32, [U64, U64, U64]),
+    "luxb200_share_ksk": (INT, [VP, VP]),
     "luxb200_evalbingate_multi_batch": (INT, [VP, INT, U32, VP, VP, VP, VP, U64, U64]),
     "luxb200_bootstrap_batch": (INT, [VP, VP, VP, VP, VP, U64, U64, INT]),
     "luxb200_evalfunc_batch": (INT, [VP, VP, VP, VP, U64, U64, VP, VP, U64, U64]),

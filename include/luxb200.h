@@ -125,6 +125,23 @@ int luxb200_bootstrap_batch(luxb200_ctx* ctx, const uint64_t* a, const uint64_t*
 /* lut [lutlen] over Z_ctmod (GenerateLUTviaFunction, binfhecontext.cpp:372-387); beta = BinFHEContext::GetBeta() */
 int luxb200_evalfunc_batch(luxb200_ctx* ctx, const uint64_t* a, const uint64_t* b, const uint64_t* lut,
                            uint64_t lutlen, uint64_t beta, uint64_t* oa, uint64_t* ob, uint64_t count, uint64_t ctmod);
+/* ---- large-precision floor / sign / digit decomposition (binfhe-base-scheme.cpp:335-521) ----------------------------
+ * Ciphertexts a [count][n] mod `mod` (the large plaintext-space modulus, a power of two up to 2^29, binfhecontext.cpp:60),
+ * beta = BinFHEContext::GetBeta().  One context per gadget base: ctxs[0] is the current base (RingGSWParams->GetBaseG()),
+ * the others are the rest of the reference's key map (BTKeyGen with timeOptimization fills baseG = 2^14, 2^18, 2^27,
+ * binfhecontext.cpp:292-298); n_ctx == 3 switches bases with the shrinking modulus exactly as :415-434 does. */
+int luxb200_evalfloor_batch(luxb200_ctx* ctx, const uint64_t* a, const uint64_t* b, uint64_t* oa, uint64_t* ob, uint64_t count,
+                            uint64_t mod, uint64_t beta, uint32_t roundbits);
+int luxb200_evalsign_batch(luxb200_ctx* const* ctxs, int n_ctx, const uint64_t* a, const uint64_t* b, uint64_t* oa,
+                           uint64_t* ob, uint64_t count, uint64_t mod, uint64_t beta, int scheme_switch);
+/* out_a [n_out][count][n], out_b [n_out][count], out_mod [n_out] (modulus of each returned digit ciphertext);
+ * n_out = luxb200_evaldecomp_count(q, mod, beta) <= max_out */
+int luxb200_evaldecomp_batch(luxb200_ctx* const* ctxs, int n_ctx, const uint64_t* a, const uint64_t* b, uint64_t* out_a,
+                             uint64_t* out_b, uint64_t* out_mod, uint32_t max_out, uint32_t* n_out, uint64_t count,
+                             uint64_t mod, uint64_t beta);
+uint32_t luxb200_evaldecomp_count(uint64_t q, uint64_t mod, uint64_t beta);
+/* dst borrows src's device copy of the switching key (contexts that differ in baseG only) */
+int luxb200_share_ksk(luxb200_ctx* dst, luxb200_ctx* src);
 /* a [count][n] mod amod; acc [count][2][N] EVALUATION format, in place */
 int luxb200_blind_rotate_batch(luxb200_ctx* ctx, const uint64_t* a, uint64_t amod, uint64_t* acc, uint64_t count);
 /* backend::Backend::ExternalProductBatch (backend.h:185-194): RGSW x RLWE -> RLWE as one AddToAccDM step computes it

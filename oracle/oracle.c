@@ -785,6 +785,107 @@ int orc_evalfunc(OrcCtx* c, const u64* a, const u64* b, const u64* lut, u64 lutl
         if (evalfunc_one(c, a + i * n, b[i], lut, lutlen, beta, ctmod, oa + i * n, ob + i)) rc = -1;
     return rc;
 }
+/* ---- large precision: EvalFloor / EvalSign / EvalDecomp (binfhe-base-scheme.cpp:335-521) ------------------------- */
+u64 orc_ctx_baseG(OrcCtx* c) { return c->baseG; }
+/* binfhe-base-scheme.cpp:335-377; ciphertext (a, b) mod `mod`, in place */
+static void floor_one(OrcCtx* c, u64* a, u64* b, u64 mod, u64 beta, u64 qs) {
+    u32 n = c->n;
+    u64* w = malloc(sizeof(u64) * (2 * (n + 1) + qs));
+    u64 *r = w + n + 1, *f = r + n + 1;
+    *b = addmod(*b, beta % mod, mod);                              /* EvalAddConstEq(ct1, beta) */
+    for (int pass = 0; pass < 2; ++pass) {
+        for (u32 i = 0; i < n; ++i) w[i] = a[i] % qs;              /* ct1Modq: SetModulus(q) */
+        u64 wb = *b % qs, rb;
+        for (u64 x = 0; x < qs; ++x) {
+            if (pass == 0) f[x] = x < (qs >> 1) ? mod - (qs >> 2) : (qs >> 2);
+            else f[x] = x < (qs >> 2) ? mod - (qs >> 1) - x : (x < 3 * (qs >> 2) ? x : mod + (qs >> 1) - x);
+        }
+        bootstrap_func(c, w, wb, qs, f, mod, r, &rb);
+        for (u32 i = 0; i < n; ++i) a[i] = submod(a[i], r[i], mod); /* EvalSubEq(ct1, ct2) */
+        *b = submod(*b, rb, mod);
+    }
+    free(w);
+}
+int orc_evalfloor(OrcCtx* c, const u64* a, const u64* b, u64* oa, u64* ob, u64 count, u64 mod, u64 beta, u32 roundbits,
+                  int threads) {
+    u32 n = c->n;
+    u64 qs = roundbits == 0 ? c->q : beta * ((u64)1 << (roundbits + 1));
+#pragma omp parallel for num_threads(threads > 0 ? threads : 1) schedule(dynamic)
+    for (u64 i = 0; i < count; ++i) {
+        memcpy(oa + i * n, a + i * n, sizeof(u64) * n);
+        ob[i] = b[i];
+        floor_one(c, oa + i * n, ob + i, mod, beta, qs);
+    }
+    return 0;
+}
+static OrcCtx* find_base(OrcCtx** cs, int ncs, u64 base) {
+    for (int i = 0; i < ncs; ++i) if (cs[i]->baseG == base) return cs[i];
+    return NULL;
+}
+static u64 dynamic_base(u64 mod, int sign_variant) {
+    u32 binLog = sign_variant ? (u32)ceil((double)(64 - __builtin_clzll(mod)) - 1) : (u32)ceil(log2((double)mod));
+    if (binLog <= 17) return (u64)1 << 27;
+    if (binLog <= 26) return (u64)1 << 18;
+    return 0;
+}
+u32 orc_evaldecomp_count(u64 q, u64 mod, u64 beta) {
+    u32 k = 1;
+    while (mod > q && k < 64) { mod = mod / q * 2 * beta; ++k; }
+    return k;
+}
+/* what 0: EvalSign (:380-455), 1: EvalSign(schemeSwitch), 2: EvalDecomp (:458-521; out [k][count][n], out_mod [k]).
+ * cs[0] = the context of the current gadget base; ncs == 3 = the reference's dynamic mode. Returns outputs per input. */
+int orc_evalsign_decomp(OrcCtx** cs, int ncs, const u64* a, const u64* b, u64* oa, u64* ob, u64* out_mod, u64 count,
+                        u64 mod0, u64 beta, int what, int threads) {
+    OrcCtx* c0 = cs[0];
+    u32 n = c0->n;
+    u64 q = c0->q;
+    if (mod0 <= q) return -1;
+    int rc = what == 2 ? (int)orc_evaldecomp_count(q, mod0, beta) : 1;
+#pragma omp parallel for num_threads(threads > 0 ? threads : 1) schedule(dynamic)
+    for (u64 i = 0; i < count; ++i) {
+        u64* t = malloc(sizeof(u64) * (n + 1));
+        memcpy(t, a + i * n, sizeof(u64) * n);
+        u64 tb = b[i], mod = mod0;
+        OrcCtx* cur = c0;
+        u32 k = 0;
+        while (mod > q) {
+            if (what == 2) {
+                for (u32 j = 0; j < n; ++j) oa[((u64)k * count + i) * n + j] = t[j] % q;
+                ob[(u64)k * count + i] = tb % q;
+                if (i == 0) out_mod[k] = q;
+                ++k;
+            }
+            floor_one(cur, t, &tb, mod, beta, q);
+            u64 mod_new = what == 2 ? mod / q * 2 * beta : (mod << 1) * beta / q;
+            for (u32 j = 0; j < n; ++j) t[j] = round_qQ(t[j], mod_new, mod);   /* ModSwitch(mod, cttmp) */
+            tb = round_qQ(tb, mod_new, mod);
+            mod = mod_new;
+            if (ncs == 3) {
+                u64 base = dynamic_base(mod, what != 2);
+                if (base != 0) { OrcCtx* nx = find_base(cs, ncs, base); if (nx) cur = nx; }
+            }
+        }
+        if (what == 2) {
+            memcpy(oa + ((u64)k * count + i) * n, t, sizeof(u64) * n);
+            ob[(u64)k * count + i] = tb;
+            if (i == 0) out_mod[k] = mod;
+        } else {
+            tb = addmod(tb, beta % mod, mod);
+            u64* f = malloc(sizeof(u64) * mod);
+            for (u64 x = 0; x < mod; ++x) {
+                int low = x < mod / 2;
+                f[x] = ((what == 0) == low) ? q / 4 : q - q / 4;
+            }
+            bootstrap_func(cur, t, tb, mod, f, q, oa + i * n, ob + i);
+            if (what == 0) ob[i] = submod(ob[i], q >> 2, q);        /* EvalSubConstEq(cttmp, q >> 2) */
+            free(f);
+        }
+        free(t);
+    }
+    return rc;
+}
+
 double orc_time_bingate(OrcCtx* c, int gate, const u64* a1, const u64* b1, const u64* a2, const u64* b2, u64* oa,
                         u64* ob, u64 count, int threads) {
     struct timespec t0, t1;

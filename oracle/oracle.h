@@ -69,6 +69,13 @@ int orc_bootstrap(OrcCtx*, const uint64_t* a, const uint64_t* b, uint64_t* oa, u
                   uint64_t p, int extended, int threads);
 int orc_evalfunc(OrcCtx*, const uint64_t* a, const uint64_t* b, const uint64_t* lut, uint64_t lutlen, uint64_t beta,
                  uint64_t* oa, uint64_t* ob, uint64_t count, uint64_t ctmod, int threads);
+/* large precision (binfhe-base-scheme.cpp:335-521): ciphertexts (n, mod); one context per gadget base, cs[0] current */
+uint64_t orc_ctx_baseG(OrcCtx*);
+int orc_evalfloor(OrcCtx*, const uint64_t* a, const uint64_t* b, uint64_t* oa, uint64_t* ob, uint64_t count, uint64_t mod,
+                  uint64_t beta, uint32_t roundbits, int threads);
+uint32_t orc_evaldecomp_count(uint64_t q, uint64_t mod, uint64_t beta);
+int orc_evalsign_decomp(OrcCtx** cs, int ncs, const uint64_t* a, const uint64_t* b, uint64_t* oa, uint64_t* ob,
+                        uint64_t* out_mod, uint64_t count, uint64_t mod, uint64_t beta, int what, int threads);
 double orc_time_bingate(OrcCtx*, int gate, const uint64_t* a1, const uint64_t* b1, const uint64_t* a2,
                         const uint64_t* b2, uint64_t* oa, uint64_t* ob, uint64_t count, int threads);
 int orc_max_threads(void);

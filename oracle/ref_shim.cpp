@@ -442,6 +442,125 @@ int ref_dcrt_switchformat(uint32_t N, uint32_t L, uint32_t bits, uint64_t* data,
     return 0;
 }
 
+
+// ---- large-precision contexts (binfhecontext.cpp:53-104) and EvalFloor / EvalSign / EvalDecomp -----------------------
+void* ref_ctx_create_largeprec(int paramset, int arbFunc, uint32_t logQ, uint32_t N, int timeOpt) {
+    try {
+        auto* h = new RefCtx();
+        h->cc.GenerateBinFHEContext(static_cast<BINFHE_PARAMSET>(paramset), arbFunc != 0, logQ, N, GINX, timeOpt != 0);
+        return h;
+    }
+    catch (...) {
+        return nullptr;
+    }
+}
+// gadget bases of the key map after BTKeyGen (binfhecontext.cpp:292-306); returns the count
+int ref_btkey_bases(void* hv, uint32_t* out, int max) {
+    auto* h = static_cast<RefCtx*>(hv);
+    int k   = 0;
+    auto map = h->cc.GetBTKeyMap();   // a copy held for the loop (the accessor returns a temporary)
+    for (auto& kv : *map)
+        if (k < max)
+            out[k++] = kv.first;
+    return k;
+}
+static RingGSWBTKey key_of_base(RefCtx* h, uint32_t baseG) {
+    return h->cc.GetBTKeyMap()->at(baseG);   // by value: shared_ptr members keep the key objects alive
+}
+int ref_bsk_entry_base(void* hv, uint32_t baseG, uint32_t i0, uint32_t i1, uint32_t i2, uint64_t* out) {
+    auto* h        = static_cast<RefCtx*>(hv);
+    const RingGSWBTKey key = key_of_base(h, baseG);
+    const auto& ek = key.BSkey->GetElements();
+    const auto& e  = ek[i0][i1][i2];
+    if (!e)
+        return 0;
+    const auto& el = e->GetElements();
+    size_t pos     = 0;
+    for (auto& row : el)
+        for (auto& poly : row) {
+            uint32_t N = poly.GetLength();
+            for (uint32_t k = 0; k < N; ++k)
+                out[pos++] = poly[k].ConvertToInt();
+        }
+    return static_cast<int>(el.size());
+}
+int ref_ksk_dump_base(void* hv, uint32_t baseG, uint64_t* A, uint64_t* B) {
+    auto* h        = static_cast<RefCtx*>(hv);
+    const RingGSWBTKey key = key_of_base(h, baseG);
+    const auto& ks = key.KSkey;
+    const auto& kA = ks->GetElementsA();
+    const auto& kB = ks->GetElementsB();
+    size_t pa = 0, pb = 0;
+    for (size_t i = 0; i < kA.size(); ++i)
+        for (size_t j = 0; j < kA[i].size(); ++j)
+            for (size_t k = 0; k < kA[i][j].size(); ++k) {
+                const auto& v = kA[i][j][k];
+                for (uint32_t t = 0; t < v.GetLength(); ++t)
+                    A[pa++] = v[t].ConvertToInt();
+                B[pb++] = kB[i][j][k].ConvertToInt();
+            }
+    return 0;
+}
+uint32_t ref_current_baseG(void* hv) {
+    return static_cast<RefCtx*>(hv)->cc.GetParams()->GetRingGSWParams()->GetBaseG();
+}
+int ref_evalfloor(void* hv, const uint64_t* a, const uint64_t* b, uint64_t* oa, uint64_t* ob, uint64_t count, uint64_t mod,
+                  uint32_t roundbits, int threads) {
+    auto* h    = static_cast<RefCtx*>(hv);
+    uint32_t n = h->cc.GetParams()->GetLWEParams()->Getn();
+    int rc     = 0;
+#pragma omp parallel for num_threads(threads > 0 ? threads : 1) schedule(dynamic)
+    for (uint64_t i = 0; i < count; ++i) {
+        try {
+            auto r = h->cc.EvalFloor(make_ct(a + i * n, b[i], n, mod), roundbits);
+            put_ct(r, oa + i * n, ob + i);
+        }
+        catch (...) {
+            rc = -1;
+        }
+    }
+    return rc;
+}
+// EvalSign mutates the shared RingGSW parameters (Change_BaseG): one ciphertext at a time
+int ref_evalsign(void* hv, const uint64_t* a, const uint64_t* b, uint64_t* oa, uint64_t* ob, uint64_t count, uint64_t mod,
+                 int schemeSwitch) {
+    auto* h    = static_cast<RefCtx*>(hv);
+    uint32_t n = h->cc.GetParams()->GetLWEParams()->Getn();
+    try {
+        for (uint64_t i = 0; i < count; ++i) {
+            auto r = h->cc.EvalSign(make_ct(a + i * n, b[i], n, mod), schemeSwitch != 0);
+            put_ct(r, oa + i * n, ob + i);
+        }
+    }
+    catch (...) {
+        return -1;
+    }
+    return 0;
+}
+// out_a [k][count][n], out_b [k][count], out_mod [k]; returns the number of ciphertexts per input (or -1)
+int ref_evaldecomp(void* hv, const uint64_t* a, const uint64_t* b, uint64_t* out_a, uint64_t* out_b, uint64_t* out_mod,
+                   uint32_t max_out, uint64_t count, uint64_t mod) {
+    auto* h    = static_cast<RefCtx*>(hv);
+    uint32_t n = h->cc.GetParams()->GetLWEParams()->Getn();
+    int k      = -1;
+    try {
+        for (uint64_t i = 0; i < count; ++i) {
+            auto v = h->cc.EvalDecomp(make_ct(a + i * n, b[i], n, mod));
+            if (v.size() > max_out)
+                return -1;
+            k = static_cast<int>(v.size());
+            for (size_t d = 0; d < v.size(); ++d) {
+                put_ct(v[d], out_a + (d * count + i) * n, out_b + d * count + i);
+                out_mod[d] = v[d]->GetModulus().ConvertToInt();
+            }
+        }
+    }
+    catch (...) {
+        return -1;
+    }
+    return k;
+}
+
 // ---- CPU baseline timers (bench.py --impl reference / cpu_baseline) --------------------------------
 // `count` EvalBinGate(gate) on count ciphertext pairs, outer OMP loop over independent gates — the shape
 // of EvalBinGateBatch (src/binfhe/lib/batch/batch.cpp:197-200). Returns seconds.

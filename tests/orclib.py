@@ -76,6 +76,10 @@ def oracle():
         _sig(L.orc_evalbingate_multi, INT, [VP, INT, U32, VP, VP, VP, VP, U64, U64, INT])
         _sig(L.orc_bootstrap, INT, [VP, VP, VP, VP, VP, U64, U64, INT, INT])
         _sig(L.orc_evalfunc, INT, [VP, VP, VP, VP, U64, U64, VP, VP, U64, U64, INT])
+        _sig(L.orc_ctx_baseG, U64, [VP])
+        _sig(L.orc_evalfloor, INT, [VP, VP, VP, VP, VP, U64, U64, U64, U32, INT])
+        _sig(L.orc_evaldecomp_count, U32, [U64, U64, U64])
+        _sig(L.orc_evalsign_decomp, INT, [VP, INT, VP, VP, VP, VP, VP, U64, U64, U64, INT, INT])
         _sig(L.orc_time_bingate, C.c_double, [VP, INT, VP, VP, VP, VP, VP, VP, U64, INT])
         _sig(L.orc_max_threads, INT, [])
         _oracle = L
@@ -117,6 +121,14 @@ def ref():
         _sig(L.ref_ntt, INT, [U64, U64, U32, VP, U64, INT, INT])
         _sig(L.ref_dcrt_chain, INT, [U32, U32, U32, VP, VP])
         _sig(L.ref_dcrt_switchformat, INT, [U32, U32, U32, VP, U64, INT])
+        _sig(L.ref_ctx_create_largeprec, VP, [INT, INT, U32, U32, INT])
+        _sig(L.ref_btkey_bases, INT, [VP, VP, INT])
+        _sig(L.ref_bsk_entry_base, INT, [VP, U32, U32, U32, U32, VP])
+        _sig(L.ref_ksk_dump_base, INT, [VP, U32, VP, VP])
+        _sig(L.ref_current_baseG, U32, [VP])
+        _sig(L.ref_evalfloor, INT, [VP, VP, VP, VP, VP, U64, U64, U32, INT])
+        _sig(L.ref_evalsign, INT, [VP, VP, VP, VP, VP, U64, U64, INT])
+        _sig(L.ref_evaldecomp, INT, [VP, VP, VP, VP, VP, VP, U32, U64, U64])
         _sig(L.ref_time_bingate, C.c_double, [VP, INT, VP, VP, VP, VP, VP, VP, U64, INT])
         _sig(L.ref_time_ntt, C.c_double, [U64, U64, U32, VP, U64, INT, INT])
         _sig(L.ref_max_threads, INT, [])
@@ -149,10 +161,14 @@ class Params:
 class RefContext:
     """The reference's BinFHEContext with keys, plus flat dumps of its keys in the canonical layout."""
 
-    def __init__(self, paramset, method, custom=None):
-        """custom = (bits, cyclOrder, n, q, modKS, baseKS, baseG, baseR, numAutoKeys, keyDist) for a hand-made set."""
+    def __init__(self, paramset, method, custom=None, largeprec=None):
+        """custom = (bits, cyclOrder, n, q, modKS, baseKS, baseG, baseR, numAutoKeys, keyDist) for a hand-made set;
+        largeprec = (arbFunc, logQ, N, timeOptimization): GenerateBinFHEContext(set, arbFunc, logQ, N, GINX, timeOpt),
+        binfhecontext.cpp:53-104 (set TOY or STD128)."""
         self.L = ref()
-        if custom is not None:
+        if largeprec is not None:
+            self.h = self.L.ref_ctx_create_largeprec(PARAMSET[paramset], *[int(x) for x in largeprec])
+        elif custom is not None:
             self.h = self.L.ref_ctx_create_custom(*custom, METHOD[method])
         else:
             self.h = self.L.ref_ctx_create(PARAMSET[paramset], METHOD[method])
@@ -200,6 +216,30 @@ class RefContext:
         B = np.zeros(p.ksk_rows(), np.uint64)
         self.L.ref_ksk_dump(self.h, P(A), P(B))
         return A, B
+
+    def bases(self):
+        """gadget bases of the key map (one after a plain BTKeyGen, three with timeOptimization)"""
+        out = np.zeros(4, np.uint32)
+        k = self.L.ref_btkey_bases(self.h, P(out), 4)
+        return [int(x) for x in out[:k]]
+
+    def dump_keys_of_base(self, baseG):
+        """(bsk, kskA, kskB, Params) of the key set generated for gadget base `baseG` (GINX layout)"""
+        import copy, math
+        p = copy.copy(self.p)
+        p.baseG = baseG
+        p.digitsG = int(math.ceil(math.log(float(p.Q)) / math.log(float(baseG))))
+        p.rows = 2 * (p.digitsG - 1)
+        rg = p.rows * 2 * p.N
+        bsk = np.zeros(p.bsk_len(), np.uint64)
+        for i in range(p.n):
+            for s in range(2):
+                off = (i * 2 + s) * rg
+                assert self.L.ref_bsk_entry_base(self.h, baseG, 0, s, i, P(bsk[off:off + rg])) == p.rows
+        A = np.zeros(p.ksk_rows() * p.n, np.uint64)
+        B = np.zeros(p.ksk_rows(), np.uint64)
+        self.L.ref_ksk_dump_base(self.h, baseG, P(A), P(B))
+        return bsk, A, B, p
 
     def encrypt(self, m, pmod=4, mod=None):
         p = self.p

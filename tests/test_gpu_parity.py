@@ -540,3 +540,60 @@ def test_wide_custom_params_all_methods(method, bits, N, baseG, qKS):
         O.orc_keyswitch(oc.h, P(np.ascontiguousarray(ka[i])), int(kb[i]), P(xa), P(xb))
         assert (oa[i] == xa).all() and ob[i] == xb[0]
     ctx.close(); oc.close()
+
+
+@pytest.mark.parametrize("logQ,time_opt", [(17, True), (27, True), (23, False), (13, False)])
+def test_largeprec_floor_sign_decomp(logQ, time_opt):
+    """EvalFloor / EvalSign / EvalDecomp (binfhe-base-scheme.cpp:335-521) on the large-precision contexts of
+    binfhecontext.cpp:53-104 (TOY lattice: Q = LastPrime(54, 4096), N = 2048, qKS = 2^35, one key set per gadget base): the
+    UnitTestFunc.cpp:45-266 cases — messages around p/2 at Q = 2^logQ — bit for bit against the oracle (itself pinned to the
+    reference for exactly these calls, tests/test_oracle_vs_reference.py), and the decrypted sign."""
+    import ctypes as C
+    from fhe_b200 import context as cx
+    O = oracle()
+    ctxs = cx.GenerateLargePrecisionContexts("TOY", False, logQ, 0, time_opt)
+    assert len(ctxs) == (3 if time_opt else 1)
+    ocs, sk = [], None
+    for c in ctxs:
+        oc = oracle_twin(c, "GINX")
+        if sk is None:
+            sk, bsk, A, B = oc.keygen(seed=5)
+        else:
+            # another key set for the same secret key: re-run keygen with the same seed (same sk stream first)
+            sk2, bsk, A, B = oc.keygen(seed=5)
+            assert (sk2 == sk).all()
+        c.BTKeyLoad(bsk, A, B)
+        ocs.append(oc)
+    c0, o0 = ctxs[0], ocs[0]
+    Qbig, q, beta = 1 << logQ, c0.q, c0.GetBeta()
+    pl = (q // (2 * beta)) * (Qbig // q)
+    cnt = 8
+    a = np.zeros((cnt, c0.n), np.uint64); b = np.zeros(cnt, np.uint64)
+    for i in range(cnt):
+        a[i], b[i] = o0.encrypt(sk, pl // 2 + i - 4, 700 + i, pmod=pl, mod=Qbig)
+    arr = (C.c_void_p * len(ocs))(*[oc.h for oc in ocs])
+    (oa, ob), res = c0.EvalFloorBatch((a, b), Qbig)
+    assert res.success, res.error
+    xa = np.zeros_like(a); xb = np.zeros_like(b)
+    assert O.orc_evalfloor(o0.h, P(a), P(b), P(xa), P(xb), cnt, Qbig, beta, 0, 8) == 0
+    assert (oa == xa).all() and (ob == xb).all()
+    for ss in (False, True):
+        (oa, ob), res = cx.EvalSignBatch(ctxs, (a, b), Qbig, ss)
+        assert res.success, res.error
+        assert O.orc_evalsign_decomp(arr, len(ocs), P(a), P(b), P(xa), P(xb), None, cnt, Qbig, beta, int(ss), 8) == 1
+        assert (oa == xa).all() and (ob == xb).all(), ss
+    (oa, ob), res = cx.EvalSignBatch(ctxs, (a, b), Qbig)
+    assert [o0.decrypt(sk, oa[i], ob[i], 2, q) for i in range(cnt)] == [int(i >= 4) for i in range(cnt)]
+    (da, db, dm), res = cx.EvalDecompBatch(ctxs, (a, b), Qbig)
+    assert res.success, res.error
+    k = len(dm)
+    ya = np.zeros_like(da); yb = np.zeros_like(db); ym = np.zeros_like(dm)
+    assert O.orc_evalsign_decomp(arr, len(ocs), P(a), P(b), P(ya), P(yb), P(ym), cnt, Qbig, beta, 2, 8) == k
+    assert (dm == ym).all() and (da == ya).all() and (db == yb).all()
+    # small-precision input is refused with the reference's message
+    (_, _), res = cx.EvalSignBatch(ctxs, (a % np.uint64(q), b % np.uint64(q)), q)
+    assert not res.success and "only for large precision" in res.error
+    for c in ctxs:
+        c.close()
+    for oc in ocs:
+        oc.close()

@@ -115,3 +115,61 @@ def test_wide_regime_pins_the_oracle(method, bits, cyc, baseG):
     O.orc_bootstrap(oc.h, P(a1), P(b1), P(xa), P(xb), cnt, 4, 0, 4)
     assert (oa == xa).all() and (ob == xb).all()
     rc.close(); oc.close()
+
+
+def _largeprec_pair(logQ, time_opt, arb=False):
+    """reference large-precision context (TOY lattice, binfhecontext.cpp:53-104) + one oracle context per gadget base of
+    its key map, loaded with the reference's own keys; contexts ordered current base first"""
+    rc = RefContext("TOY", "GINX", largeprec=(arb, logQ, 0, time_opt))
+    rc.keygen()
+    cur = orclib.ref().ref_current_baseG(rc.h)
+    bases = rc.bases()
+    assert cur in bases and len(bases) == (3 if time_opt and logQ != 11 else 1)
+    ocs = []
+    for bg in [cur] + [x for x in bases if x != cur]:
+        bsk, A, B, p = rc.dump_keys_of_base(bg)
+        oc = OrcContext(p)
+        assert oc.p.digitsG == p.digitsG and oc.p.Q == rc.p.Q and oc.p.psi == rc.p.psi
+        oc.load(bsk, A, B)
+        ocs.append(oc)
+    return rc, ocs
+
+
+@pytest.mark.parametrize("logQ,time_opt", [(17, True), (23, False), (27, True), (13, False)])
+def test_largeprec_floor_sign_decomp_pin_the_oracle(logQ, time_opt):
+    """EvalFloor / EvalSign / EvalDecomp (binfhe-base-scheme.cpp:335-521; the cases of UnitTestFunc.cpp:45-266: messages
+    around p/2 at Q = 2^logQ) — the reference's ciphertexts against the oracle's, coefficient for coefficient, with one
+    key and with the three-key dynamic mode."""
+    import ctypes as C
+    R, O = orclib.ref(), orclib.oracle()
+    rc, ocs = _largeprec_pair(logQ, time_opt)
+    p = rc.p
+    Qbig, q, beta = 1 << logQ, p.q, R.ref_get_beta(rc.h)
+    pl = (q // (2 * beta)) * (Qbig // q)      # GetMaxPlaintextSpace() * factor
+    cnt = 6
+    a = np.zeros((cnt, p.n), np.uint64); b = np.zeros(cnt, np.uint64)
+    for i in range(cnt):
+        a[i], b[i] = rc.encrypt(pl // 2 + i - 3, pl, Qbig)
+    arr = (C.c_void_p * len(ocs))(*[oc.h for oc in ocs])
+    # floor (current base only)
+    oa = np.zeros_like(a); ob = np.zeros_like(b); xa = oa.copy(); xb = ob.copy()
+    assert R.ref_evalfloor(rc.h, P(a), P(b), P(oa), P(ob), cnt, Qbig, 0, 4) == 0
+    assert O.orc_evalfloor(ocs[0].h, P(a), P(b), P(xa), P(xb), cnt, Qbig, beta, 0, 4) == 0
+    assert (oa == xa).all() and (ob == xb).all()
+    # sign, both encodings
+    for ss in (0, 1):
+        assert R.ref_evalsign(rc.h, P(a), P(b), P(oa), P(ob), cnt, Qbig, ss) == 0
+        assert O.orc_evalsign_decomp(arr, len(ocs), P(a), P(b), P(xa), P(xb), None, cnt, Qbig, beta, ss, 4) == 1
+        assert (oa == xa).all() and (ob == xb).all(), ss
+    assert R.ref_evalsign(rc.h, P(a), P(b), P(oa), P(ob), cnt, Qbig, 0) == 0
+    assert [rc.decrypt(oa[i], ob[i], 2, q) for i in range(cnt)] == [int(i >= 3) for i in range(cnt)]
+    # digit decomposition
+    k = O.orc_evaldecomp_count(q, Qbig, beta)
+    da = np.zeros((k, cnt, p.n), np.uint64); db = np.zeros((k, cnt), np.uint64); dm = np.zeros(k, np.uint64)
+    ya = da.copy(); yb = db.copy(); ym = dm.copy()
+    assert R.ref_evaldecomp(rc.h, P(a), P(b), P(da), P(db), P(dm), k, cnt, Qbig) == k
+    assert O.orc_evalsign_decomp(arr, len(ocs), P(a), P(b), P(ya), P(yb), P(ym), cnt, Qbig, beta, 2, 4) == k
+    assert (dm == ym).all() and (da == ya).all() and (db == yb).all()
+    rc.close()
+    for oc in ocs:
+        oc.close()
