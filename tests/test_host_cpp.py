@@ -46,8 +46,11 @@ def _run_parity(args, timeout=1500):
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
     res = json.loads(r.stdout.strip().splitlines()[-1])
     assert res["failed_checks"] == 0
-    for k in ["BootstrapBatch", "EvalCMUXBatch", "BatchDAG_levels", "GreaterThan8_circuit", "Backend_BlindRotateBatch",
-              "Backend_ExternalProductBatch", "Backend_KeySwitchBatch", "Backend_ModSwitchBatch", "Backend_PackUnpackBSK"] + NEW_CHECKS:
+    keys = ["BootstrapBatch", "EvalCMUXBatch", "BatchDAG_levels", "Backend_BlindRotateBatch", "Backend_ExternalProductBatch",
+            "Backend_KeySwitchBatch", "Backend_ModSwitchBatch", "Backend_PackUnpackBSK"] + NEW_CHECKS
+    if int(args[2]) > 0:
+        keys.append("GreaterThan8_circuit")
+    for k in keys:
         assert res[k] is True, k
     return res, r.stdout
 
