@@ -226,12 +226,13 @@ class BinFHEContext:
 
     # -- device-resident operators (uint32 tensors already in HBM; pointers as ints) ------------------------
     # -- gate circuits (BatchDAG, binfhe-batch.h:255-279) ------------------------------------------------
-    def EvalCircuitBatch(self, n_inputs, gates, outputs, in_a, in_b):
+    def EvalCircuitBatch(self, n_inputs, gates, outputs, in_a, in_b, luts=None):
         """One circuit over `count` independent input sets, level-scheduled on the device with device-resident
-        intermediates (luxb200_circuit_batch).  gates: [(op, in0, in1)], op a 2-input gate name, "NOT" or "BOOTSTRAP";
+        intermediates (luxb200_circuit_batch[_ex]).  gates: [(op, in0, in1)], op a 2-input gate name, "NOT", "BOOTSTRAP" or
+        "EVALFUNC" (in1 = index into `luts`, a list of length-q tables as GenerateLUTviaFunction returns them);
         wire ids as BatchDAG hands them out (inputs 0..n_inputs-1, then one per gate).  in_a [n_inputs][count][n],
         in_b [n_inputs][count]; returns ((out_a [n_outputs][count][n], out_b [n_outputs][count]), BatchResult)."""
-        ops = {"NOT": 100, "BOOTSTRAP": 101}
+        ops = {"NOT": 100, "BOOTSTRAP": 101, "EVALFUNC": 102}
         g = np.zeros((max(len(gates), 1), 3), np.uint32)
         for k, (op, i0, i1) in enumerate(gates):
             g[k] = (ops[op] if op in ops else _l.GATE[op], i0, i1 if i1 is not None else 0)
@@ -241,8 +242,10 @@ class BinFHEContext:
         cnt = in_b.shape[1]
         oa = np.empty((len(outs), cnt, self.n), np.uint64)
         ob = np.empty((len(outs), cnt), np.uint64)
-        rc = self.L.luxb200_circuit_batch(self.h, n_inputs, _l.ptr(g), len(gates), _l.ptr(outs), len(outs), _l.ptr(in_a),
-                                          _l.ptr(in_b), _l.ptr(oa), _l.ptr(ob), cnt)
+        lt = self._u64(np.stack(luts)) if luts else None
+        rc = self.L.luxb200_circuit_batch_ex(self.h, n_inputs, _l.ptr(g), len(gates), _l.ptr(outs), len(outs),
+                                             _l.ptr(lt) if lt is not None else None, len(luts) if luts else 0, self.GetBeta(),
+                                             _l.ptr(in_a), _l.ptr(in_b), _l.ptr(oa), _l.ptr(ob), cnt)
         return (oa, ob), self._result(rc, len(gates) * cnt)
 
     def CircuitStats(self):

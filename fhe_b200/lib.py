@@ -74,6 +74,7 @@ SIGNATURES = {
     "luxb200_ntt_last_ms": (C.c_float, [VP]),
     "luxb200_evalbingate_batch_dev": (INT, [VP, INT, VP, VP, VP, VP, VP, VP, U64]),
     "luxb200_circuit_batch": (INT, [VP, U32, VP, U32, VP, U32, VP, VP, VP, VP, U64]),
+    "luxb200_circuit_batch_ex": (INT, [VP, U32, VP, U32, VP, U32, VP, U32, U64, VP, VP, VP, VP, U64]),
     "luxb200_circuit_last_stats": (INT, [VP, VP]),
     "luxb200_last_timing": (INT, [VP, VP]),
     "luxb200_launch_count": (U64, [VP]),

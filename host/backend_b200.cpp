@@ -640,14 +640,21 @@ void BackendB200::Bootstrap(const std::vector<LWECiphertext>& in, std::vector<LW
 }
 
 void BackendB200::EvalCircuit(const std::vector<LWECiphertext>& inputs, const std::vector<luxb200_gate>& gates,
-                              const std::vector<uint32_t>& outputs, std::vector<LWECiphertext>& out) {
+                              const std::vector<uint32_t>& outputs, const std::vector<std::vector<NativeInteger>>& luts,
+                              const NativeInteger& beta, std::vector<LWECiphertext>& out) {
     if (outputs.empty()) { out.clear(); return; }
     std::lock_guard<std::recursive_mutex> lk(mu_);
     std::vector<uint64_t> a(inputs.size() * size_t(p_.n)), b(inputs.size()), oa(outputs.size() * size_t(p_.n)), ob(outputs.size());
     flatten_cts_to(inputs.data(), inputs.size(), p_.n, p_.q, a.data(), b.data());   // [n_inputs][count = 1][n]
-    check(luxb200_circuit_batch(h_, static_cast<uint32_t>(inputs.size()), gates.data(), static_cast<uint32_t>(gates.size()),
-                                outputs.data(), static_cast<uint32_t>(outputs.size()), a.data(), b.data(), oa.data(), ob.data(),
-                                1), "EvalCircuit");
+    std::vector<uint64_t> lt(luts.size() * size_t(p_.q));
+    for (size_t i = 0; i < luts.size(); ++i) {
+        if (luts[i].size() != p_.q) throw std::invalid_argument("BackendB200::EvalCircuit: a look-up table must have q entries");
+        for (size_t k = 0; k < luts[i].size(); ++k) lt[i * p_.q + k] = u64(luts[i][k]);
+    }
+    check(luxb200_circuit_batch_ex(h_, static_cast<uint32_t>(inputs.size()), gates.data(), static_cast<uint32_t>(gates.size()),
+                                   outputs.data(), static_cast<uint32_t>(outputs.size()), lt.empty() ? nullptr : lt.data(),
+                                   static_cast<uint32_t>(luts.size()), u64(beta), a.data(), b.data(), oa.data(), ob.data(), 1),
+          "EvalCircuit");
     build_cts(oa, ob, p_.n, NativeInteger(p_.q), NativeInteger(4), out);
 }
 

@@ -91,8 +91,10 @@ public:
                   std::vector<LWECiphertext>& out);
     // A gate DAG in one call (luxb200_circuit_batch, count = 1): wires 0 .. inputs.size()-1 are `inputs`, wire
     // inputs.size() + g the result of gates[g]; out[k] = wire outputs[k].  Intermediates stay on the device.
+    // LUXB200_OP_EVALFUNC gates name a table of `luts` (BatchDAG::AddEvalFunc nodes); beta = cc.GetBeta().
     void EvalCircuit(const std::vector<LWECiphertext>& inputs, const std::vector<luxb200_gate>& gates,
-                     const std::vector<uint32_t>& outputs, std::vector<LWECiphertext>& out);
+                     const std::vector<uint32_t>& outputs, const std::vector<std::vector<NativeInteger>>& luts,
+                     const NativeInteger& beta, std::vector<LWECiphertext>& out);
 
     // host time (ms) the last gate-level call spent packing inputs / building outputs, and inside the C ABI call
     struct Timing { double pack_ms = 0, call_ms = 0, unpack_ms = 0; };

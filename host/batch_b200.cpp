@@ -6,9 +6,10 @@
 // not a fallback): without that flag a missing or unbound B200 backend is an error, never a silent CPU path.
 //
 // BatchDAG::Execute (sequential in the reference, batch.cpp:429-482) is a level scheduler here.  A DAG made of 2-input
-// gates, Bootstrap and CMUX over plaintext-modulus-4 ciphertexts mod q goes to the device as ONE luxb200_circuit_batch
-// call (levels scheduled there, intermediates resident in HBM); anything else (EvalFunc nodes, other moduli) is levelled
-// on the host and every level issued as one batched call per (operation, gate | LUT).
+// gates, Bootstrap, CMUX and EvalFunc nodes over ciphertexts mod q goes to the device as ONE luxb200_circuit_batch_ex
+// call (levels scheduled there, intermediates resident in HBM); anything else (other ciphertext moduli, a Bootstrap of a
+// ciphertext whose plaintext modulus is not 4) is levelled on the host and every level issued as one batched call per
+// (operation, gate | LUT).
 #include <algorithm>
 #include <future>
 #include <map>
@@ -213,23 +214,30 @@ static bool execute_on_device(BinFHEContext& cc, std::vector<LWECiphertext>& cts
     const NativeInteger q = cc.GetParams()->GetLWEParams()->Getq();
     std::vector<char> produced(cts.size(), 0);
     for (const auto& op : ops) {
-        if (op.type == BatchOp::OP_BINGATE ? !gate2(op.gate) : (op.type != BatchOp::OP_BOOTSTRAP && op.type != BatchOp::OP_CMUX))
+        if (op.type == BatchOp::OP_BINGATE ? !gate2(op.gate)
+                                           : (op.type != BatchOp::OP_BOOTSTRAP && op.type != BatchOp::OP_CMUX && op.type != BatchOp::OP_EVAL_FUNC))
             return false;
+        if (op.type == BatchOp::OP_EVAL_FUNC && op.lut.size() != q.ConvertToInt<size_t>()) return false;
         produced[op.output_ids[0]] = 1;
     }
     // wires: the DAG's input ciphertexts first, then one wire per gate (CMUX = NOT + 3 NAND, binfhe-base-scheme.cpp:176-183)
+    // pmod: the plaintext modulus a wire's ciphertext carries.  Only Bootstrap reads it (the offset Q/(2p)+1,
+    // binfhe-base-scheme.cpp:214); gates and EvalFunc return fresh ciphertexts (m_p = 4), Bootstrap hands its input's on.
     std::vector<uint32_t> wire(cts.size(), 0);
+    std::vector<uint64_t> pmod(cts.size(), 4);
     std::vector<LWECiphertext> inputs;
     for (size_t id = 0; id < cts.size(); ++id) {
         if (produced[id]) continue;
         if (!cts[id]) return false;   // never referenced or a caller error: the per-operation path reports it
-        if (cts[id]->GetModulus() != q || cts[id]->GetptModulus() != NativeInteger(4)) return false;
+        if (cts[id]->GetModulus() != q) return false;
+        pmod[id] = cts[id]->GetptModulus().ConvertToInt<uint64_t>();
         wire[id] = static_cast<uint32_t>(inputs.size());
         inputs.push_back(cts[id]);
     }
     if (inputs.empty()) return false;
     std::vector<luxb200_gate> gates;
     std::vector<uint32_t> outs;
+    std::vector<std::vector<NativeInteger>> luts;   // distinct tables of the EvalFunc nodes
     const uint32_t ni = static_cast<uint32_t>(inputs.size());
     auto emit = [&](uint32_t op, uint32_t a, uint32_t b) {
         gates.push_back(luxb200_gate{op, a, b});
@@ -242,7 +250,13 @@ static bool execute_on_device(BinFHEContext& cc, std::vector<LWECiphertext>& cts
         if (op.type == BatchOp::OP_BINGATE) {
             w = emit(static_cast<uint32_t>(op.gate), wire[op.input_ids[0]], wire[op.input_ids[1]]);
         } else if (op.type == BatchOp::OP_BOOTSTRAP) {
+            if (pmod[op.input_ids[0]] != 4) return false;   // the device circuit bootstraps with p = 4
             w = emit(LUXB200_OP_BOOTSTRAP, wire[op.input_ids[0]], 0);
+        } else if (op.type == BatchOp::OP_EVAL_FUNC) {
+            size_t li = 0;
+            while (li < luts.size() && luts[li] != op.lut) ++li;
+            if (li == luts.size()) luts.push_back(op.lut);
+            w = emit(LUXB200_OP_EVALFUNC, wire[op.input_ids[0]], static_cast<uint32_t>(li));
         } else {   // EvalBinGate(CMUX, {v0, v1, v2}) = NAND(NAND(v0, NOT v2), NAND(v1, v2))
             const uint32_t v0 = wire[op.input_ids[0]], v1 = wire[op.input_ids[1]], v2 = wire[op.input_ids[2]];
             const uint32_t t  = emit(LUXB200_OP_NOT, v2, 0);
@@ -250,10 +264,11 @@ static bool execute_on_device(BinFHEContext& cc, std::vector<LWECiphertext>& cts
             w = emit(NAND, n1, n2);
         }
         wire[op.output_ids[0]] = w;
+        pmod[op.output_ids[0]] = 4;
         outs.push_back(w);
     }
     std::vector<LWECiphertext> res;
-    b200(cc)->EvalCircuit(inputs, gates, outs, res);
+    b200(cc)->EvalCircuit(inputs, gates, outs, luts, cc.GetBeta(), res);
     for (size_t i = 0; i < ops.size(); ++i) cts[ops[i].output_ids[0]] = res[i];
     result.processed = ops.size();
     return true;

@@ -239,15 +239,15 @@ int main(int argc, char** argv) {
         report("BatchDAG_levels", og.size(), bad);
     }
 
-    // ---- BatchDAG with an EvalFunc node: not a gate circuit, so Execute levels it on the host (one batched call per level
-    // and operation kind) — same results as the reference's sequential walk
+    // ---- BatchDAG with EvalFunc nodes: one device circuit too (luxb200_circuit_batch_ex) — same results as the reference's
+    // sequential walk (batch.cpp:429-482)
     if (!dag_lut.empty()) {
         auto build = [&](BatchDAG& d, std::vector<size_t>& outs, const std::vector<LWECiphertext>& fin) {
             for (size_t i = 0; i + 1 < cnt; i += 2) {
                 size_t a = d.AddCiphertext(c1[i]), b = d.AddCiphertext(c2[i + 1]), e = d.AddCiphertext(fin[i]);
                 size_t x = d.AddBinGate(NAND, a, b), f = d.AddEvalFunc(e, dag_lut), y = d.AddBinGate(XNOR, x, b);
-                size_t u = d.AddBootstrap(y);
-                outs.insert(outs.end(), {x, f, y, u});
+                size_t u = d.AddBootstrap(y), f2 = d.AddEvalFunc(f, dag_lut);   // a function of a function
+                outs.insert(outs.end(), {x, f, y, u, f2});
             }
         };
         std::vector<LWECiphertext> fin(cnt);

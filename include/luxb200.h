@@ -198,7 +198,7 @@ uint64_t luxb200_launch_count(luxb200_ctx* ctx);
  * launch over every (gate, input set) pair of the level, mixed gate kinds included.  Every intermediate ciphertext stays in
  * HBM; only the inputs go up and the wires listed in `outputs` come back.
  * in_a [n_inputs][count][n], in_b [n_inputs][count] mod q; out_a [n_outputs][count][n], out_b [n_outputs][count]. */
-enum { LUXB200_OP_NOT = 100, LUXB200_OP_BOOTSTRAP = 101 };
+enum { LUXB200_OP_NOT = 100, LUXB200_OP_BOOTSTRAP = 101, LUXB200_OP_EVALFUNC = 102 };
 typedef struct {
     uint32_t op;         /* BINGATE code or LUXB200_OP_* */
     uint32_t in0, in1;   /* wire ids; in1 ignored by the 1-input ops */
@@ -206,6 +206,15 @@ typedef struct {
 int luxb200_circuit_batch(luxb200_ctx* ctx, uint32_t n_inputs, const luxb200_gate* gates, uint32_t n_gates,
                           const uint32_t* outputs, uint32_t n_outputs, const uint64_t* in_a, const uint64_t* in_b,
                           uint64_t* out_a, uint64_t* out_b, uint64_t count);
+/* The same with BatchOp::OP_EVAL_FUNC nodes (BatchDAG::AddEvalFunc, batch.cpp:455-460): op = LUXB200_OP_EVALFUNC,
+ * in0 = the input wire, in1 = index of the node's look-up table in `luts` [n_luts][q] (values over Z_q as
+ * GenerateLUTviaFunction writes them, binfhecontext.cpp:372-387); beta = BinFHEContext::GetBeta().  Per node exactly
+ * BinFHEScheme::EvalFunc (binfhe-base-scheme.cpp:241-332): a negacyclic table is one bootstrap, a periodic or arbitrary one
+ * two chained bootstraps (two levels); an arbitrary table with q > N is refused with the reference's message. */
+int luxb200_circuit_batch_ex(luxb200_ctx* ctx, uint32_t n_inputs, const luxb200_gate* gates, uint32_t n_gates,
+                             const uint32_t* outputs, uint32_t n_outputs, const uint64_t* luts, uint32_t n_luts,
+                             uint64_t beta, const uint64_t* in_a, const uint64_t* in_b, uint64_t* out_a, uint64_t* out_b,
+                             uint64_t count);
 /* out[0] = dependency levels, out[1] = bootstrapped gates, out[2] = kernel launches of the last circuit call */
 int luxb200_circuit_last_stats(luxb200_ctx* ctx, uint64_t* out);
 

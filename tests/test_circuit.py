@@ -161,3 +161,59 @@ def test_circuit_helpers_cpu():
                            np.zeros((1, 200), np.int64)])
     rev = lambda v: sum(((v >> i) & 1) << (7 - i) for i in range(8))
     assert (plain_circuit(gates, bits)[out] == (rev(va) > rev(vb))).all()
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("name,method,cnt", [("TOY", "GINX", 4), ("TOY", "LMKCDEY", 3), ("STD128", "GINX", 2), ("STD128_LMKCDEY", "LMKCDEY", 2)])
+def test_circuit_with_evalfunc_nodes(name, method, cnt):
+    """BatchDAG with OP_EVAL_FUNC nodes (batch.cpp:455-460) mixed with gates, NOT and Bootstrap as ONE device call: a
+    negacyclic table (1 bootstrap), a periodic one (2 chained bootstraps) and — where q <= N — an arbitrary one (2 bootstraps
+    at modulus 2q), feeding each other and gates; every wire against the oracle applied node by node
+    (BinFHEScheme::EvalFunc, binfhe-base-scheme.cpp:241-332).  An arbitrary table with q > N is refused like the reference."""
+    from fhe_b200.context import BinFHEContext
+    ctx = BinFHEContext().GenerateBinFHEContext(name, method)
+    oc = oracle_twin(ctx, method)
+    sk, bsk, A, B = oc.keygen(seed=9, key_dist=getattr(ctx, "keyDist", 0))
+    ctx.BTKeyLoad(bsk, A, B)
+    q, p = ctx.q, 4
+    neg = ctx.GenerateLUTviaFunction(lambda x, pp: x + 1 if x < pp // 2 else pp - (x - pp // 2 + 1), p)
+    per = ctx.GenerateLUTviaFunction(lambda x, pp: x % (pp // 2), p)
+    arb = ctx.GenerateLUTviaFunction(lambda x, pp: (x * x + 1) % pp, p)
+    luts = [neg, per] + ([arb] if q <= ctx.N else [])
+    n_inputs = 3
+    in_a = np.zeros((n_inputs, cnt, ctx.n), np.uint64); in_b = np.zeros((n_inputs, cnt), np.uint64)
+    for i in range(n_inputs):
+        for k in range(cnt):
+            in_a[i, k], in_b[i, k] = oc.encrypt(sk, (i + k) % p, 100 * i + k, pmod=p)
+    # wires: 0 1 2 inputs; 3 = f_neg(0); 4 = f_per(1); 5 = AND(3, 4); 6 = f_per(5); 7 = NOT 6; 8 = XOR(7, 2); 9 = BOOT(4);
+    # 10 = f_neg(4) (a function of a function); [11 = f_arb(2); 12 = f_per(11); 13 = NAND(11, 0)]
+    gates = [("EVALFUNC", 0, 0), ("EVALFUNC", 1, 1), ("AND", 3, 4), ("EVALFUNC", 5, 1), ("NOT", 6, None), ("XOR", 7, 2),
+             ("BOOTSTRAP", 4, None), ("EVALFUNC", 4, 0)]
+    if len(luts) == 3:
+        gates += [("EVALFUNC", 2, 2), ("EVALFUNC", 11, 1), ("NAND", 11, 0)]
+    outs = list(range(n_inputs + len(gates)))
+    (oa, ob), res = ctx.EvalCircuitBatch(n_inputs, gates, outs, in_a, in_b, luts)
+    assert res.success, res.error
+    wa = [in_a[i] for i in range(n_inputs)]; wb = [in_b[i] for i in range(n_inputs)]
+    for op, i0, i1 in gates:
+        a0, b0 = np.ascontiguousarray(wa[i0]), np.ascontiguousarray(wb[i0])
+        if op == "EVALFUNC":
+            lut64 = np.ascontiguousarray(luts[i1], np.uint64)
+            a = np.zeros_like(a0); b = np.zeros(cnt, np.uint64)
+            assert oc.L.orc_evalfunc(oc.h, P(a0), P(b0), P(lut64), len(lut64), ctx.GetBeta(), P(a), P(b), cnt, q, 4) == 0
+        elif op == "NOT":
+            a = np.where(a0 == 0, 0, q - a0).astype(np.uint64); b = ((q // 4 + q - b0) % q).astype(np.uint64)
+        elif op == "BOOTSTRAP":
+            a = np.zeros_like(a0); b = np.zeros(cnt, np.uint64)
+            oc.L.orc_bootstrap(oc.h, P(a0), P(b0), P(a), P(b), cnt, 4, 0, 4)
+        else:
+            a, b = oc.evalbingate(op, a0, b0, np.ascontiguousarray(wa[i1]), np.ascontiguousarray(wb[i1]))
+        wa.append(a); wb.append(b)
+    for w in outs:
+        assert (oa[w] == wa[w]).all() and (ob[w] == wb[w]).all(), (name, method, w)
+    st = ctx.CircuitStats()
+    assert st["bootstrapped_gates"] == sum({"EVALFUNC": None, "NOT": 0}.get(g[0], 1) if g[0] != "EVALFUNC" else (1 if g[2] == 0 else 2) for g in gates)
+    if q > ctx.N:   # arbitrary table: refused with the reference's message (binfhe-base-scheme.cpp:264-268)
+        (_, _), res = ctx.EvalCircuitBatch(n_inputs, [("EVALFUNC", 0, 0)], [3], in_a, in_b, [arb])
+        assert not res.success and "ring dimension" in res.error
+    ctx.close(); oc.close()
