@@ -178,7 +178,7 @@ def test_circuit_with_evalfunc_nodes(name, method, cnt):
     q, p = ctx.q, 4
     neg = ctx.GenerateLUTviaFunction(lambda x, pp: x + 1 if x < pp // 2 else pp - (x - pp // 2 + 1), p)
     per = ctx.GenerateLUTviaFunction(lambda x, pp: x % (pp // 2), p)
-    arb = ctx.GenerateLUTviaFunction(lambda x, pp: (x * x + 1) % pp, p)
+    arb = ctx.GenerateLUTviaFunction(lambda x, pp: (x * x * x + 1) % pp, p)   # 1, 2, 1, 0: neither negacyclic nor periodic
     luts = [neg, per] + ([arb] if q <= ctx.N else [])
     n_inputs = 3
     in_a = np.zeros((n_inputs, cnt, ctx.n), np.uint64); in_b = np.zeros((n_inputs, cnt), np.uint64)

@@ -149,3 +149,30 @@ def test_packed_keys_load_on_b200(pset, cnt):
     assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
     assert "B200 gates on LoadPacked keys == reference" in r.stdout
     assert json.loads(r.stdout.strip().splitlines()[-1])["failed_checks"] == 0
+
+
+LARGEPREC = os.path.join(BUILD, "largeprec_parity")
+
+
+@pytest.mark.gpu
+@needs_build
+@pytest.mark.parametrize("logQ,time_opt", [(17, 1), (27, 1), (23, 0)])
+def test_largeprec_batch_layer_matches_reference(logQ, time_opt):
+    """host/largeprec_b200: EvalFloorBatch / EvalSignBatch / EvalDecompBatch on the reference's own large-precision context
+    (keys from BTKeyGen — three key sets with timeOptimization — and Encrypt at Q = 2^logQ) vs cc.EvalFloor / EvalSign /
+    EvalDecomp (binfhecontext.cpp:346-370), ciphertext for ciphertext."""
+    r = subprocess.run([LARGEPREC, "TOY", str(logQ), str(time_opt), "8"], capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stdout[-3000:] + r.stderr[-2000:]
+    res = json.loads(r.stdout.strip().splitlines()[-1])
+    assert res["failed_checks"] == 0 and res["key_sets"] == (3 if time_opt else 1)
+    for k in ["EvalFloorBatch", "EvalSignBatch", "EvalSignBatch_schemeSwitch", "EvalDecompBatch", "EvalSignBatch_refuses_small"]:
+        assert res[k] is True, k
+
+
+@needs_build
+def test_largeprec_layer_refuses_without_gpu():
+    from conftest import has_gpu
+    if has_gpu():
+        pytest.skip("GPU present")
+    r = subprocess.run([LARGEPREC, "TOY", "13", "0", "2"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 3 and "no CPU fallback" in r.stdout
