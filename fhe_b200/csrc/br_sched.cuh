@@ -174,7 +174,12 @@ br_sched_kernel(const __grid_constant__ BrParams P) {
         const u32 op = op_next;
         if ((op & OP_MASK) == OP_END) done = true;
         op_next = done ? (u32)OP_END : ops[pc + 1];
+#ifdef LB_SCHED_PAIRBAR   // A/B build: warp pairs advance on their own (named barrier per ciphertext slot)
+        pair_barrier(1 + slot);
+        if (done) break;
+#else
         if (__syncthreads_and(done)) break;
+#endif
         const u32 ty = done ? (u32)OP_END : (op & OP_MASK), arg = op & ~OP_MASK;
         u32 dg[ND][E];
         if (ty == OP_AUTO || (ty == OP_PERM1 && c == 1))   // EVALUATION-format automorphism of the accumulator
@@ -187,7 +192,11 @@ br_sched_kernel(const __grid_constant__ BrParams P) {
         // warp 1 waits at the barrier and then adds sum_d digit_d * ak[d][1] from warp 0's published rows.
         if (ty == OP_EXT || (ty == OP_AUTO && c == 0))
             digits_from_acc<LOGN, LOGH, ROWS>(acc, dg, P, scratch, sm.twB, sm.twiB, exch, c, lane);
+#ifdef LB_SCHED_PAIRBAR
+        pair_barrier(1 + slot);
+#else
         __syncthreads();
+#endif
         if (ty == OP_EXT) {
             mac_replace<LOGN, ROWS>(acc, dg, exch, P, P.bsk + (size_t)arg * kblock, c, lane);
         } else if (ty == OP_AUTO) {
