@@ -127,6 +127,24 @@ class BinFHEContext:
         _l.check(self.L.luxb200_load_bsk(self.h, _l.ptr(bsk), int(on_device)))
         _l.check(self.L.luxb200_load_ksk(self.h, _l.ptr(kskA), _l.ptr(kskB), int(on_device)))
 
+    def BTKeyGen(self, sk, seed, want_skN=False):
+        """BinFHEContext::BTKeyGen (binfhecontext.cpp:285-307) on the device: sk = LWE secret (n signed values); the ring
+        secret, the switching key and the refresh key are drawn on the GPU (ChaCha20 streams from `seed`) straight into
+        the packed layouts.  Not bit-equal to the reference's Blake2-seeded keys; same structure and noise."""
+        sk = np.ascontiguousarray(sk, np.int64)
+        assert sk.shape == (self.n,)
+        skN = np.zeros(self.N, np.int64) if want_skN else None
+        _l.check(self.L.luxb200_btkeygen(self.h, _l.ptr(sk), int(seed) & (2**64 - 1), _l.ptr(skN) if want_skN else None))
+        return skN
+
+    def ExportKeys(self):
+        """(bsk, kskA, kskB) of the resident keys in the canonical flat uint64 layouts."""
+        bsk = np.empty(self.bsk_len(), np.uint64)
+        A = np.empty(self.ksk_rows() * self.n, np.uint64)
+        B = np.empty(self.ksk_rows(), np.uint64)
+        _l.check(self.L.luxb200_export_keys(self.h, _l.ptr(bsk), _l.ptr(A), _l.ptr(B)))
+        return bsk, A, B
+
     # -- batched operators (host buffers) -----------------------------------------------------------------
     def _u64(self, x):
         return np.ascontiguousarray(x, dtype=np.uint64)

@@ -5,6 +5,7 @@
 #include "aux_kernels.cuh"
 #include "br_sched.cuh"
 #include "br_wide.cuh"
+#include "keygen.cuh"
 #include "ntt_kernels.cuh"
 
 thread_local std::string g_last_error;
@@ -82,6 +83,51 @@ int Ntt32Tables::build(uint32_t N_, uint64_t Q_, uint64_t psi_) {
     return 0;
 }
 
+// (w, Shoup) twiddle tables, psi powers and reduction constants of the shared-memory kernels (br_wide.cuh, keygen.cuh);
+// W.wsize must be set (4: Q < 2^30, 8 otherwise)
+int lb_build_wide_tables(luxb200_ctx* c) {
+    using namespace lb;
+    luxb200_ctx::Wide& W = c->wide;
+    if (W.tw.p) return 0;
+    const luxb200_params* p = &c->p;
+    const uint32_t N = p->N;
+        const uint64_t Q = p->Q;
+        std::vector<uint64_t> tw, twi, pw(2 * (size_t)N);
+        ntt_tables(N, Q, c->p.psi, tw, twi);
+        pw[0] = 1;
+        for (uint32_t i = 1; i < 2 * N; ++i) pw[i] = mulmod(pw[i - 1], c->p.psi, Q);
+        W.ninv = invmod_prime(N % Q, Q);
+    int rcw = 0;
+        if (W.wsize == 8) {
+            W.ninv_s = shoup64(W.ninv, Q);
+            W.mu = (uint64_t)((((u128_t)1) << 64) / Q);
+            W.r = (uint64_t)((((u128_t)1) << 64) % Q);
+            W.rs = shoup64(W.r, Q);
+            std::vector<ulonglong2> t(N), ti(N);
+            for (uint32_t i = 0; i < N; ++i) { t[i] = make_ulonglong2(tw[i], shoup64(tw[i], Q)); ti[i] = make_ulonglong2(twi[i], shoup64(twi[i], Q)); }
+            rcw = W.tw.ensure(N * 16); if (!rcw) rcw = W.twi.ensure(N * 16); if (!rcw) rcw = W.pw.ensure(2 * (size_t)N * 8);
+            if (!rcw && (cudaMemcpy(W.tw.p, t.data(), N * 16, cudaMemcpyHostToDevice) != cudaSuccess ||
+                         cudaMemcpy(W.twi.p, ti.data(), N * 16, cudaMemcpyHostToDevice) != cudaSuccess ||
+                         cudaMemcpy(W.pw.p, pw.data(), 2 * (size_t)N * 8, cudaMemcpyHostToDevice) != cudaSuccess))
+                rcw = lb_fail(LUXB200_ERR_CUDA, "table upload failed");
+        } else {
+            W.ninv_s = shoup32(W.ninv, Q);
+            W.mu = (uint64_t)((1ull << 32) / Q);
+            W.r = (uint64_t)((1ull << 32) % Q);
+            W.rs = shoup32(W.r, Q);
+            std::vector<uint2> t(N), ti(N);
+            std::vector<u32> pw32(2 * (size_t)N);
+            for (uint32_t i = 0; i < N; ++i) { t[i] = make_uint2((u32)tw[i], shoup32(tw[i], Q)); ti[i] = make_uint2((u32)twi[i], shoup32(twi[i], Q)); }
+            for (uint32_t i = 0; i < 2 * N; ++i) pw32[i] = (u32)pw[i];
+            rcw = W.tw.ensure(N * 8); if (!rcw) rcw = W.twi.ensure(N * 8); if (!rcw) rcw = W.pw.ensure(2 * (size_t)N * 4);
+            if (!rcw && (cudaMemcpy(W.tw.p, t.data(), N * 8, cudaMemcpyHostToDevice) != cudaSuccess ||
+                         cudaMemcpy(W.twi.p, ti.data(), N * 8, cudaMemcpyHostToDevice) != cudaSuccess ||
+                         cudaMemcpy(W.pw.p, pw32.data(), 2 * (size_t)N * 4, cudaMemcpyHostToDevice) != cudaSuccess))
+                rcw = lb_fail(LUXB200_ERR_CUDA, "table upload failed");
+        }
+    return rcw;
+}
+
 extern "C" {
 
 const char* luxb200_last_error(void) { return g_last_error.c_str(); }
@@ -130,40 +176,7 @@ int luxb200_ctx_create(const luxb200_params* p, int device, luxb200_ctx** out) {
         const uint32_t N = p->N;
         W.smem = (size_t)(2 + c->rows) * (N + N / 16) * W.wsize;
         if (W.smem > 232448 || N < 256) { luxb200_ctx_destroy(c); return lb_fail(LUXB200_ERR_UNSUPPORTED, "N = %u with %u digit polynomials does not fit in shared memory", N, c->rows); }
-        const uint64_t Q = p->Q;
-        std::vector<uint64_t> tw, twi, pw(2 * (size_t)N);
-        ntt_tables(N, Q, c->p.psi, tw, twi);
-        pw[0] = 1;
-        for (uint32_t i = 1; i < 2 * N; ++i) pw[i] = mulmod(pw[i - 1], c->p.psi, Q);
-        W.ninv = invmod_prime(N % Q, Q);
-        int rcw = 0;
-        if (W.wsize == 8) {
-            W.ninv_s = shoup64(W.ninv, Q);
-            W.mu = (uint64_t)((((u128_t)1) << 64) / Q);
-            W.r = (uint64_t)((((u128_t)1) << 64) % Q);
-            W.rs = shoup64(W.r, Q);
-            std::vector<ulonglong2> t(N), ti(N);
-            for (uint32_t i = 0; i < N; ++i) { t[i] = make_ulonglong2(tw[i], shoup64(tw[i], Q)); ti[i] = make_ulonglong2(twi[i], shoup64(twi[i], Q)); }
-            rcw = W.tw.ensure(N * 16); if (!rcw) rcw = W.twi.ensure(N * 16); if (!rcw) rcw = W.pw.ensure(2 * (size_t)N * 8);
-            if (!rcw && (cudaMemcpy(W.tw.p, t.data(), N * 16, cudaMemcpyHostToDevice) != cudaSuccess ||
-                         cudaMemcpy(W.twi.p, ti.data(), N * 16, cudaMemcpyHostToDevice) != cudaSuccess ||
-                         cudaMemcpy(W.pw.p, pw.data(), 2 * (size_t)N * 8, cudaMemcpyHostToDevice) != cudaSuccess))
-                rcw = lb_fail(LUXB200_ERR_CUDA, "table upload failed");
-        } else {
-            W.ninv_s = shoup32(W.ninv, Q);
-            W.mu = (uint64_t)((1ull << 32) / Q);
-            W.r = (uint64_t)((1ull << 32) % Q);
-            W.rs = shoup32(W.r, Q);
-            std::vector<uint2> t(N), ti(N);
-            std::vector<u32> pw32(2 * (size_t)N);
-            for (uint32_t i = 0; i < N; ++i) { t[i] = make_uint2((u32)tw[i], shoup32(tw[i], Q)); ti[i] = make_uint2((u32)twi[i], shoup32(twi[i], Q)); }
-            for (uint32_t i = 0; i < 2 * N; ++i) pw32[i] = (u32)pw[i];
-            rcw = W.tw.ensure(N * 8); if (!rcw) rcw = W.twi.ensure(N * 8); if (!rcw) rcw = W.pw.ensure(2 * (size_t)N * 4);
-            if (!rcw && (cudaMemcpy(W.tw.p, t.data(), N * 8, cudaMemcpyHostToDevice) != cudaSuccess ||
-                         cudaMemcpy(W.twi.p, ti.data(), N * 8, cudaMemcpyHostToDevice) != cudaSuccess ||
-                         cudaMemcpy(W.pw.p, pw32.data(), 2 * (size_t)N * 4, cudaMemcpyHostToDevice) != cudaSuccess))
-                rcw = lb_fail(LUXB200_ERR_CUDA, "table upload failed");
-        }
+        int rcw = lb_build_wide_tables(c);
         if (rcw) { luxb200_ctx_destroy(c); return rcw; }
     }
     int rc = 0;

@@ -118,6 +118,7 @@ struct luxb200_ctx {
 };
 
 int lb_set_device(int device);
+int lb_build_wide_tables(luxb200_ctx* c);
 #define LB_LOCK(c) std::lock_guard<std::recursive_mutex> lb_guard_((c)->mu)
 
 // ---- entry points of api.cu used by circuit.cu (a separate translation unit, same library) -------------------

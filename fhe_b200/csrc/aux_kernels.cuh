@@ -31,6 +31,14 @@ __global__ void pack_ksk_kernel(const u64* __restrict__ in, KT* __restrict__ out
     const u32 k = (u32)(idx % npad);
     out[idx] = k < n ? (KT)in[row * n + k] : (KT)0;
 }
+template <typename KT>
+__global__ void unpack_ksk_kernel(const KT* __restrict__ in, u64* __restrict__ out, u32 n, u32 npad, u64 rows) {
+    const u64 idx = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= rows * n) return;
+    const u64 row = idx / n;
+    const u32 k = (u32)(idx % n);
+    out[idx] = (u64)in[row * npad + k];
+}
 __global__ void narrow_u64_u32_kernel(const u64* __restrict__ in, u32* __restrict__ out, u64 total) {
     const u64 idx = (u64)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx < total) out[idx] = (u32)in[idx];

@@ -43,6 +43,8 @@ SIGNATURES = {
     "luxb200_ksk_len": (U64, [VP]),
     "luxb200_load_bsk": (INT, [VP, VP, INT]),
     "luxb200_load_ksk": (INT, [VP, VP, VP, INT]),
+    "luxb200_btkeygen": (INT, [VP, VP, U64, VP]),
+    "luxb200_export_keys": (INT, [VP, VP, VP, VP]),
     "luxb200_synchronize": (INT, [VP]),
     "luxb200_evalbingate_batch": (INT, [VP, INT, VP, VP, VP, VP, VP, VP, U64, INT]),
     "luxb200_evalbingate_batch_ex": (INT, [VP, INT, VP, VP, VP, VP, VP, VP, U64, INT, U64, INT]),

@@ -93,6 +93,13 @@ uint64_t luxb200_ksk_len(luxb200_ctx* ctx);   /* elements of KSK A (B has ksk_le
  * (e.g. the receive buffer of an NCCL broadcast) */
 int luxb200_load_bsk(luxb200_ctx* ctx, const uint64_t* bsk, int on_device);
 int luxb200_load_ksk(luxb200_ctx* ctx, const uint64_t* A, const uint64_t* B, int on_device);
+/* BinFHEContext::BTKeyGen (binfhecontext.cpp:285-307; KeySwitchGen lwe-pke.cpp:264-344, KeyGenAcc rgsw-acc-{cggi,dm,
+ * lmkcdey}.cpp) on the device, straight into the packed key layouts.  sk [n] signed LWE secret, seed = caller entropy
+ * (ChaCha20 streams); skN_out [N] optional (the ring secret).  Keys are NOT bit-equal to reference-generated ones (other
+ * PRNG); they have the same structure and noise distribution and interoperate: luxb200_export_keys returns them in the
+ * canonical layouts, which the reference's evaluator accepts through BTKeyLoad. */
+int luxb200_btkeygen(luxb200_ctx* ctx, const int64_t* sk, uint64_t seed, int64_t* skN_out);
+int luxb200_export_keys(luxb200_ctx* ctx, uint64_t* bsk, uint64_t* kskA, uint64_t* kskB);
 int luxb200_synchronize(luxb200_ctx* ctx);
 /* One-time key exchange inside one process (the only exchange step of the path): ctxs[0] holds the keys,
  * ctxs[1..n-1] (same parameters, other GPUs of the box) receive the packed device images peer-to-peer over

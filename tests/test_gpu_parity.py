@@ -597,3 +597,70 @@ def test_largeprec_floor_sign_decomp(logQ, time_opt):
         c.close()
     for oc in ocs:
         oc.close()
+
+
+# ---- key generation on the device: functional + distributional parity ---------------------------------
+@pytest.mark.parametrize("name,method", [("TOY", "GINX"), ("TOY", "AP"), ("TOY", "LMKCDEY"), ("STD128", "GINX"),
+                                         ("STD128_LMKCDEY", "LMKCDEY"), ("STD256", "GINX"), ("STD192", "GINX")])
+def test_device_btkeygen(name, method):
+    """luxb200_btkeygen draws the keys on the GPU (other PRNG than the reference's Blake2: no bit-equality by nature).  Checked:
+    (1) the CPU oracle — pinned to the reference's evaluator — computes correct gates on the exported device keys, and the
+    device's own gates on them are bit-identical to the oracle's; (2) the key noise: switching-key rows b - <a, s> - msg and
+    refresh-key rows c1 - c0 * s (encryptions of 0) have mean ~ 0 and the reference's standard deviation 3.19
+    (binfhecontext.cpp:40); (3) same seed -> same keys, another seed -> other keys."""
+    from fhe_b200.context import BinFHEContext
+    O = oracle()
+    ctx = BinFHEContext().GenerateBinFHEContext(name, method)
+    rng = np.random.default_rng(17)
+    kd = getattr(ctx, "keyDist", 0)
+    sk = np.rint(rng.normal(0, 3.19, ctx.n)).astype(np.int64) if kd == 1 else rng.integers(-1, 2, ctx.n).astype(np.int64)
+    skN = ctx.BTKeyGen(sk, seed=2026, want_skN=True)
+    assert set(np.unique(skN)) <= {-1, 0, 1} and abs(skN.mean()) < 0.15
+    bsk, A, B = ctx.ExportKeys()
+    oc = oracle_twin(ctx, method)
+    oc.load(bsk, A, B)
+    cnt = 4
+    a1 = np.zeros((cnt, ctx.n), np.uint64); b1 = np.zeros(cnt, np.uint64); a2 = a1.copy(); b2 = b1.copy()
+    for i in range(cnt):
+        a1[i], b1[i] = oc.encrypt(sk, i & 1, 10 + i); a2[i], b2[i] = oc.encrypt(sk, (i >> 1) & 1, 90 + i)
+    for g, f in (("NAND", lambda x, y: 1 - (x & y)), ("XOR", lambda x, y: x ^ y)):
+        (oa, ob), res = ctx.EvalBinGateBatch(g, (a1, b1), (a2, b2))
+        assert res.success, res.error
+        xa, xb = oc.evalbingate(g, a1, b1, a2, b2, threads=os.cpu_count() or 8)
+        assert (oa == xa).all() and (ob == xb).all()
+        assert [oc.decrypt(sk, oa[i], ob[i]) for i in range(cnt)] == [f(i & 1, (i >> 1) & 1) for i in range(cnt)]
+    # (2) switching key noise on 4096 rows
+    n, N, qKS = ctx.n, ctx.N, ctx.qKS
+    rows = rng.choice(ctx.ksk_rows(), 4096, replace=False)
+    Am = A.reshape(-1, n)[rows].astype(object)
+    i_idx = rows // (ctx.baseKS * ctx.digitsKS); j_idx = (rows // ctx.digitsKS) % ctx.baseKS; k_idx = rows % ctx.digitsKS
+    inner = np.array([int(sum(int(x) * int(s) for x, s in zip(r, sk))) for r in Am[:512]], dtype=object)
+    msg = np.array([int(skN[i]) * int(j) * (ctx.baseKS ** int(k)) for i, j, k in zip(i_idx[:512], j_idx[:512], k_idx[:512])], dtype=object)
+    e = np.array([int((int(B[r]) - int(x) - int(m)) % qKS) for r, x, m in zip(rows[:512], inner, msg)], dtype=object)
+    e = np.array([int(v) - qKS if v > qKS // 2 else int(v) for v in e], dtype=np.float64)
+    assert abs(e.mean()) < 0.6 and 2.6 < e.std() < 3.8, (e.mean(), e.std())
+    # refresh key noise: GINX blocks that encrypt 0 (ek+ of s_i != 1): INTT(c1 - c0 * NTT(skN)) = e
+    if method == "GINX":
+        Q, rg = ctx.Q, ctx.rows * 2 * N
+        sN = np.array([int(v) % Q for v in skN], np.uint64).reshape(1, N).copy()
+        O.orc_ntt(Q, ctx.psi, N, P(sN), 1, 0, 1)
+        i0 = int(np.nonzero(sk != 1)[0][0])
+        blk = bsk[(2 * i0) * rg:(2 * i0 + 1) * rg].reshape(ctx.rows, 2, N)
+        errs = []
+        for r in range(ctx.rows):
+            ph = np.array([(int(c1) - int(c0) * int(s)) % Q for c0, c1, s in zip(blk[r, 0], blk[r, 1], sN[0])], np.uint64).reshape(1, N).copy()
+            O.orc_ntt(Q, ctx.psi, N, P(ph), 1, 1, 1)
+            errs += [int(v) - Q if int(v) > Q // 2 else int(v) for v in ph[0]]
+        errs = np.array(errs, np.float64)
+        assert abs(errs.mean()) < 0.4 and 2.8 < errs.std() < 3.6 and np.abs(errs).max() < 40, (errs.mean(), errs.std())
+        # rows use independent masks (the reference copies one mask to every row of a ciphertext, rgsw-acc-cggi.cpp:83)
+        assert not (blk[0, 0] == blk[2, 0]).all()
+    # (3) determinism
+    ctx2 = BinFHEContext().GenerateBinFHEContext(name, method)
+    ctx2.BTKeyGen(sk, seed=2026)
+    bsk2, A2, B2 = ctx2.ExportKeys()
+    assert (bsk2 == bsk).all() and (A2 == A).all() and (B2 == B).all()
+    ctx2.BTKeyGen(sk, seed=2027)
+    bsk3, _, _ = ctx2.ExportKeys()
+    assert not (bsk3 == bsk).all()
+    ctx.close(); ctx2.close(); oc.close()
