@@ -465,6 +465,11 @@ void BackendB200::UnpackBootstrappingKey(const DeviceBuffer& packed, RingGSWACCK
     std::vector<uint64_t> flat(luxb200_bsk_len(h_));
     if (packed.size != flat.size() * 8) throw std::invalid_argument("BackendB200::UnpackBootstrappingKey: size mismatch");
     CopyToHost(packed, flat.data(), packed.size);
+    unflatten_bsk(flat, ek);
+}
+
+// canonical flat layout -> the reference's RingGSWACCKey object graph
+void BackendB200::unflatten_bsk(const std::vector<uint64_t>& flat, RingGSWACCKey& ek) const {
     const uint32_t N = p_.N, n = p_.n;
     size_t pos = 0;
     auto take = [&]() {
@@ -677,6 +682,51 @@ void BackendB200::EvalFunc(const std::vector<LWECiphertext>& in, const std::vect
     });
     out.resize(in.size());
     build_cts_from(oa, ob, in.size(), n, NativeInteger(ctmod), NativeInteger(4), out.data());   // fresh ciphertexts: m_p = 4
+}
+
+// BinFHEContext::BTKeyGen with the keys drawn on the device (luxb200_btkeygen), then handed to the context as the
+// reference's own key objects (BTKeyLoad, binfhecontext.h:273), so cc's CPU calls and the device use the same keys.
+void BackendB200::BTKeyGen(BinFHEContext& cc, ConstLWEPrivateKey sk, uint64_t seed) {
+    if (!sk) throw std::invalid_argument("PrivateKey is empty");
+    std::lock_guard<std::recursive_mutex> lk(mu_);
+    const luxb200_params p = params_of(cc);
+    if (!h_ || std::memcmp(&p, &p_, sizeof(p)) != 0) Bind(cc);   // parameters only: the context holds no keys yet
+    const NativeVector& sv = sk->GetElement();
+    if (sv.GetLength() != p_.n) throw std::invalid_argument("BackendB200::BTKeyGen: secret key has the wrong dimension");
+    const uint64_t mod = u64(sv.GetModulus());
+    std::vector<int64_t> s(p_.n);
+    for (uint32_t i = 0; i < p_.n; ++i) {   // residues mod q -> signed values (the reference stores -1 as q - 1)
+        const uint64_t v = u64(sv[i]);
+        s[i] = v > mod / 2 ? int64_t(v) - int64_t(mod) : int64_t(v);
+    }
+    check(luxb200_btkeygen(h_, s.data(), seed, nullptr), "BTKeyGen");
+    share_keys();
+    std::vector<uint64_t> flat(luxb200_bsk_len(h_)), A(luxb200_ksk_len(h_)), B(A.size() / p_.n);
+    check(luxb200_export_keys(h_, flat.data(), A.data(), B.data()), "export_keys");
+    RingGSWBTKey key;
+    unflatten_bsk(flat, key.BSkey);
+    const uint32_t digitsKS = static_cast<uint32_t>(B.size() / (size_t(p_.N) * p_.baseKS));
+    std::vector<std::vector<std::vector<NativeVector>>> kA(p_.N);
+    std::vector<std::vector<std::vector<NativeInteger>>> kB(p_.N);
+    const NativeInteger qKS(p_.qKS);
+#pragma omp parallel for schedule(static)
+    for (uint32_t i = 0; i < p_.N; ++i) {
+        kA[i].resize(p_.baseKS);
+        kB[i].resize(p_.baseKS);
+        for (uint32_t j = 0; j < p_.baseKS; ++j)
+            for (uint32_t k = 0; k < digitsKS; ++k) {
+                const size_t row = (size_t(i) * p_.baseKS + j) * digitsKS + k;
+                NativeVector v(p_.n, qKS);
+                std::memcpy(&v[0], &A[row * p_.n], size_t(p_.n) * 8);
+                kA[i][j].push_back(std::move(v));
+                kB[i][j].push_back(NativeInteger(B[row]));
+            }
+    }
+    key.KSkey = std::make_shared<LWESwitchingKeyImpl>(std::move(kA), std::move(kB));
+    cc.BTKeyLoad(key);
+    bound_bsk_ = key.BSkey;   // these objects ARE what is resident: Attach(cc) will not reload them
+    bound_ksk_ = key.KSkey;
+    packed_bsk_ = packed_ksk_ = false;
 }
 
 BackendB200* RegisterB200(BinFHEContext& cc, const std::vector<int>& devices) {

@@ -96,6 +96,11 @@ public:
                      const std::vector<uint32_t>& outputs, const std::vector<std::vector<NativeInteger>>& luts,
                      const NativeInteger& beta, std::vector<LWECiphertext>& out);
 
+    // BinFHEContext::BTKeyGen (binfhecontext.cpp:285-307) with the refresh and switching keys generated on the device
+    // (luxb200_btkeygen; ChaCha20 streams from `seed`) and loaded back into cc as the reference's own key objects
+    // (cc.BTKeyLoad), so CPU and device evaluate with the same keys.  Not bit-equal to the reference's Blake2-drawn keys.
+    void BTKeyGen(BinFHEContext& cc, ConstLWEPrivateKey sk, uint64_t seed);
+
     // host time (ms) the last gate-level call spent packing inputs / building outputs, and inside the C ABI call
     struct Timing { double pack_ms = 0, call_ms = 0, unpack_ms = 0; };
     Timing LastTiming() const { return timing_; }
@@ -110,6 +115,7 @@ private:
     };
     void check(int rc, const char* what) const;
     void flatten_bsk(const RingGSWACCKeyImpl& ek, std::vector<uint64_t>& out) const;
+    void unflatten_bsk(const std::vector<uint64_t>& flat, RingGSWACCKey& ek) const;
     void load_keys(const RingGSWACCKey& ek, const LWESwitchingKey& ks);
     void ensure_bsk(const RingGSWACCKey& ek);
     void ensure_ksk(const LWESwitchingKey& ks);

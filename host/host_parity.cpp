@@ -123,12 +123,13 @@ static void dcrt_check(uint32_t N, uint32_t L, uint32_t bits, size_t count) {
 int main(int argc, char** argv) {
     std::vector<std::string> pos;
     size_t n_dev = 1, e2e_gates = 0;
-    bool dcrt = false;
+    bool dcrt = false, gpu_keygen = false;
     for (int i = 1; i < argc; ++i) {
         const std::string a = argv[i];
         if (a == "--devices" && i + 1 < argc) n_dev = std::strtoul(argv[++i], nullptr, 10);
         else if (a == "--e2e" && i + 1 < argc) e2e_gates = std::strtoul(argv[++i], nullptr, 10);
         else if (a == "--dcrt") dcrt = true;
+        else if (a == "--gpu-keygen") gpu_keygen = true;   // BTKeyGen on the device instead of the reference's
         else pos.push_back(a);
     }
     const std::string set = pos.size() > 0 ? pos[0] : "STD128";
@@ -149,10 +150,17 @@ int main(int argc, char** argv) {
     BinFHEContext cc;
     cc.GenerateBinFHEContext(ps, method);
     auto sk = cc.KeyGen();
-    cc.BTKeyGen(sk);
+    if (!gpu_keygen) cc.BTKeyGen(sk);
     std::vector<int> devs;
     for (size_t d = 0; d < n_dev; ++d) devs.push_back(static_cast<int>(d));
     auto* be = backend::RegisterB200(cc, devs);
+    if (gpu_keygen) {
+        // the refresh and switching keys are drawn on the B200 and loaded into cc (BTKeyLoad): every check below then runs the
+        // reference's CPU evaluator on device-generated keys against the device itself, and decrypts with the reference's sk
+        const double t0 = wall_ms();
+        be->BTKeyGen(cc, sk, 0x5eedULL + cnt);
+        std::printf("BTKeyGen on the device + hand-over to the context: %.1f ms\n", wall_ms() - t0);
+    }
     std::printf("backend: %s, %zu device(s), device memory %.1f GB, default=%s\n", be->Name().c_str(), be->NumDevices(),
                 be->DeviceMemory() / 1e9, backend::BackendTypeName(backend::CurrentBackend()->Type()).c_str());
 

@@ -66,6 +66,17 @@ def test_host_layer_matches_reference(pset, cnt, pairs):
 
 @pytest.mark.gpu
 @needs_build
+@pytest.mark.parametrize("pset,cnt,pairs", [("TOY", 12, 2), ("TOY_AP", 8, 1), ("TOY_LMKCDEY", 8, 1), ("STD128", 6, 1),
+                                            ("STD128_LMKCDEY", 6, 1)])
+def test_device_keygen_serves_the_reference(pset, cnt, pairs):
+    """BackendB200::BTKeyGen: the refresh and switching keys are generated on the B200 and handed to the reference's context
+    (BTKeyLoad).  The whole parity program then runs on them: the reference's CPU evaluator and the device agree bit for bit
+    on device-generated keys, and results decrypt correctly under the reference's secret key."""
+    _run_parity([pset, cnt, pairs, "--gpu-keygen"])
+
+
+@pytest.mark.gpu
+@needs_build
 def test_dcrtpoly_switchformat_seam():
     """host/dcrt_b200: DCRTPoly::SwitchFormat (dcrtpoly-impl.h:1953-1959) at N = 2^16, 32 limbs of 60 bits, every limb of
     the reference's own DCRTPoly objects, forward and inverse."""
