@@ -404,3 +404,40 @@ def EvalDecompBatch(ctxs, ct, mod):
     rc = c0.L.luxb200_evaldecomp_batch(_ctx_array(ctxs), len(ctxs), _l.ptr(a), _l.ptr(b), _l.ptr(oa), _l.ptr(ob), _l.ptr(om), k,
                                        C.byref(nout), cnt, mod, c0.GetBeta())
     return (oa, ob, om), c0._result(rc, cnt)
+
+
+class RNSPlan:
+    """DCRTPolyImpl::ApproxSwitchCRTBasis / ApproxModUp / ApproxModDown (dcrtpoly-impl.h:910-1030) on flat [count][limbs][N]
+    uint64 data: the basis-conversion steps of CKKS/BGV hybrid key switching either side of the DCRT NTT."""
+
+    def __init__(self, N, q, p, device=0):
+        self.L = _l.load()
+        self.q = np.ascontiguousarray(q, np.uint64)
+        self.p = np.ascontiguousarray(p, np.uint64)
+        h = _l.VP()
+        _l.check(self.L.luxb200_rns_plan_create(N, len(self.q), _l.ptr(self.q), len(self.p), _l.ptr(self.p), device, C.byref(h)))
+        self.h, self.N = h, N
+
+    def ApproxSwitchCRTBasis(self, x, direction=0):
+        x = np.ascontiguousarray(x, np.uint64)
+        cnt = x.shape[0]
+        out = np.empty((cnt, len(self.q) if direction else len(self.p), self.N), np.uint64)
+        _l.check(self.L.luxb200_approx_switch_crt_basis(self.h, _l.ptr(x), _l.ptr(out), cnt, direction))
+        return out
+
+    def ApproxModUp(self, x):
+        x = np.ascontiguousarray(x, np.uint64)
+        out = np.empty((x.shape[0], len(self.q) + len(self.p), self.N), np.uint64)
+        _l.check(self.L.luxb200_approx_mod_switch(self.h, _l.ptr(x), _l.ptr(out), x.shape[0], 0))
+        return out
+
+    def ApproxModDown(self, x):
+        x = np.ascontiguousarray(x, np.uint64)
+        out = np.empty((x.shape[0], len(self.q), self.N), np.uint64)
+        _l.check(self.L.luxb200_approx_mod_switch(self.h, _l.ptr(x), _l.ptr(out), x.shape[0], 1))
+        return out
+
+    def close(self):
+        if self.h:
+            self.L.luxb200_rns_plan_destroy(self.h)
+            self.h = None

@@ -1,0 +1,307 @@
+// rns.cu — the RNS basis-conversion steps either side of the N = 2^16 NTT in CKKS/BGV hybrid key switching:
+//   DCRTPolyImpl::ApproxSwitchCRTBasis   src/core/include/lattice/hal/default/dcrtpoly-impl.h:910-957
+//   DCRTPolyImpl::ApproxModUp            :960-986    (KeySwitchHYBRID::EvalKeySwitchPrecomputeCore, keyswitch-hybrid.cpp:328-412)
+//   DCRTPolyImpl::ApproxModDown          :988-1030   (KeySwitchHYBRID::EvalFastKeySwitchCore, keyswitch-hybrid.cpp:414-436; t = 0, CKKS)
+// out_j[k] = ( sum_i [x_i[k] * (Q/q_i)^-1]_{q_i} * [(Q/q_i)]_{p_j} ) mod p_j — the reference accumulates the products in 128 bits
+// and reduces once (BarrettUint128ModUint64); every stored value is the canonical residue, so any exact evaluation of the same
+// integer sum is bit-identical.  Tables (QHatInvModq, QHatModp, PInvModq) are derived from the moduli on the host exactly as
+// CryptoParametersRNS::PrecomputeCRTTables defines them.  HBM-resident [count][limbs][N] uint64, one thread per coefficient,
+// limb tables in shared memory; the NTTs in between are luxb200_ntt_batch_dev (ntt64_tma.inc for N >= 2^14).
+#include <algorithm>
+
+#include "api_common.h"
+#include "modarith.cuh"
+
+typedef unsigned __int128 u128;
+
+namespace {
+
+inline unsigned nblk(u64 total, unsigned per) { return (unsigned)((total + per - 1) / per); }
+
+struct RnsDev {
+    // per source limb i: modulus, (Q/q_i)^-1 mod q_i and its Shoup companion; per target limb j: modulus, floor(2^64 / p_j),
+    // 2^64 mod p_j and its Shoup companion; hat [sizeQ][sizeP] = (Q/q_i) mod p_j
+    const u64 *q, *qhatinv, *qhatinv_s, *p, *pmu, *pr, *prs, *hat;
+    u32 sizeQ, sizeP, N, pad;
+};
+
+// x [count][in_stride limbs][N] (the first sizeQ limbs are read), out [count][out_stride limbs][N] (limbs out_off .. out_off+sizeP-1)
+__global__ void __launch_bounds__(256) rns_switch_kernel(const RnsDev D, const u64* __restrict__ x, u32 in_stride, u32 in_off,
+                                                         u64* __restrict__ out, u32 out_stride, u32 out_off, u64 count) {
+    extern __shared__ u64 rns_sm[];
+    u64* hat = rns_sm;                                   // [sizeQ][sizeP]
+    u64* xh  = rns_sm + (size_t)D.sizeQ * D.sizeP;       // [sizeQ][256]
+    for (u32 t = threadIdx.x; t < D.sizeQ * D.sizeP; t += blockDim.x) hat[t] = D.hat[t];
+    const u64 gid = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool live = gid < count * D.N;
+    const u64 ct = live ? gid / D.N : 0;
+    const u32 k = (u32)(gid % D.N);
+    if (live) {
+        for (u32 i = 0; i < D.sizeQ; ++i) {
+            const u64 v = x[(ct * in_stride + in_off + i) * D.N + k];
+            const u64 qi = D.q[i];
+            u64 r = v * D.qhatinv[i] - __umul64hi(v, D.qhatinv_s[i]) * qi;   // Shoup: [0, 2 q_i)
+            r = r >= qi ? r - qi : r;
+            xh[(size_t)i * 256 + threadIdx.x] = r;
+        }
+    }
+    __syncthreads();
+    if (!live) return;
+    for (u32 j = 0; j < D.sizeP; ++j) {
+        u128 s = 0;
+        for (u32 i = 0; i < D.sizeQ; ++i) s += (u128)xh[(size_t)i * 256 + threadIdx.x] * hat[(size_t)i * D.sizeP + j];
+        const u64 pj = D.p[j], lo = (u64)s, hi = (u64)(s >> 64);
+        const u64 t = hi * D.pr[j] - __umul64hi(hi, D.prs[j]) * pj;      // hi * 2^64 mod p_j, in [0, 2 p_j)
+        const u64 l = lo - __umul64hi(lo, D.pmu[j]) * pj;                // lo mod p_j, in [0, 2 p_j)
+        u64 r = t + l;                                                   // < 4 p_j < 2^64 (p_j < 2^62)
+        r = r >= 2 * pj ? r - 2 * pj : r;
+        r = r >= pj ? r - pj : r;
+        out[(ct * out_stride + out_off + j) * D.N + k] = r;
+    }
+}
+
+// ApproxModDown tail: out_i = (x_i - s_i) * PInvModq_i mod q_i   (dcrtpoly-impl.h:1021-1028), EVALUATION format
+__global__ void rns_moddown_tail_kernel(const u64* __restrict__ x, u32 x_stride, const u64* __restrict__ s, u64* __restrict__ out,
+                                        const u64* __restrict__ q, const u64* __restrict__ pinv, const u64* __restrict__ pinv_s,
+                                        u32 sizeQ, u32 N, u64 count) {
+    const u64 gid = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (gid >= count * sizeQ * N) return;
+    const u32 k = (u32)(gid % N);
+    const u32 i = (u32)((gid / N) % sizeQ);
+    const u64 ct = gid / ((u64)N * sizeQ);
+    const u64 qi = q[i];
+    const u64 a = x[(ct * x_stride + i) * N + k], b = s[gid];
+    const u64 d = a >= b ? a - b : a + qi - b;
+    u64 r = d * pinv[i] - __umul64hi(d, pinv_s[i]) * qi;
+    out[gid] = r >= qi ? r - qi : r;
+}
+
+__global__ void rns_copy_limbs_kernel(const u64* __restrict__ in, u32 in_stride, u32 in_off, u64* __restrict__ out, u32 out_stride,
+                                      u32 out_off, u32 limbs, u32 N, u64 count) {
+    const u64 gid = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (gid >= count * limbs * N) return;
+    const u32 k = (u32)(gid % N);
+    const u32 l = (u32)((gid / N) % limbs);
+    const u64 ct = gid / ((u64)N * limbs);
+    out[(ct * out_stride + out_off + l) * N + k] = in[(ct * in_stride + in_off + l) * N + k];
+}
+
+struct Tables {
+    std::vector<u64> q, p, qhatinv, qhatinv_s, pmu, pr, prs, hat;
+};
+
+// QHatInvModq_i = ((Q / q_i) mod q_i)^-1, QHatModp[i][j] = (Q / q_i) mod p_j
+void make_tables(const u64* q, u32 sizeQ, const u64* p, u32 sizeP, Tables& T) {
+    using namespace lb;
+    T.q.assign(q, q + sizeQ); T.p.assign(p, p + sizeP);
+    T.qhatinv.resize(sizeQ); T.qhatinv_s.resize(sizeQ); T.hat.resize((size_t)sizeQ * sizeP);
+    T.pmu.resize(sizeP); T.pr.resize(sizeP); T.prs.resize(sizeP);
+    for (u32 i = 0; i < sizeQ; ++i) {
+        u64 h = 1;
+        for (u32 k = 0; k < sizeQ; ++k)
+            if (k != i) h = mulmod(h, q[k] % q[i], q[i]);
+        T.qhatinv[i] = invmod_prime(h, q[i]);
+        T.qhatinv_s[i] = shoup64(T.qhatinv[i], q[i]);
+        for (u32 j = 0; j < sizeP; ++j) {
+            u64 g = 1;
+            for (u32 k = 0; k < sizeQ; ++k)
+                if (k != i) g = mulmod(g, q[k] % p[j], p[j]);
+            T.hat[(size_t)i * sizeP + j] = g;
+        }
+    }
+    for (u32 j = 0; j < sizeP; ++j) {
+        T.pmu[j] = (u64)((((u128)1) << 64) / p[j]);
+        T.pr[j] = (u64)((((u128)1) << 64) % p[j]);
+        T.prs[j] = shoup64(T.pr[j], p[j]);
+    }
+}
+
+}  // namespace
+
+struct luxb200_rns_plan {
+    uint32_t N = 0, sizeQ = 0, sizeP = 0;
+    int device = 0;
+    Tables up, down;            // Q -> P (mod up) and P -> Q (mod down)
+    std::vector<u64> pinv, pinv_s;   // P^-1 mod q_i
+    DevBuf dev_up, dev_down, dev_tail, tmpP, tmpQ, stage_in, stage_out;
+    RnsDev d_up{}, d_down{};
+    const u64 *d_q = nullptr, *d_pinv = nullptr, *d_pinv_s = nullptr;
+    luxb200_ntt_plan *nttQ = nullptr, *nttP = nullptr;
+    cudaStream_t stream = nullptr;
+};
+
+namespace {
+
+int upload_tables(const Tables& T, DevBuf& buf, RnsDev& D, u32 N) {
+    const u32 sq = (u32)T.q.size(), sp = (u32)T.p.size();
+    std::vector<u64> flat;
+    auto push = [&](const std::vector<u64>& v) { size_t o = flat.size(); flat.insert(flat.end(), v.begin(), v.end()); return o; };
+    const size_t oq = push(T.q), oi = push(T.qhatinv), ois = push(T.qhatinv_s), op = push(T.p), omu = push(T.pmu), opr = push(T.pr),
+                 oprs = push(T.prs), oh = push(T.hat);
+    LB_TRY(buf.ensure(flat.size() * 8));
+    LB_CUDA(cudaMemcpy(buf.p, flat.data(), flat.size() * 8, cudaMemcpyHostToDevice));
+    const u64* b = buf.as<u64>();
+    D = RnsDev{b + oq, b + oi, b + ois, b + op, b + omu, b + opr, b + oprs, b + oh, sq, sp, N, 0};
+    return 0;
+}
+
+int launch_switch(luxb200_rns_plan* pl, const RnsDev& D, const u64* x, u32 in_stride, u32 in_off, u64* out, u32 out_stride,
+                  u32 out_off, u64 count) {
+    const size_t sm = ((size_t)D.sizeQ * D.sizeP + (size_t)D.sizeQ * 256) * 8;
+    if (sm > 48 * 1024) LB_CUDA(cudaFuncSetAttribute(rns_switch_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    rns_switch_kernel<<<nblk(count * D.N, 256), 256, sm, pl->stream>>>(D, x, in_stride, in_off, out, out_stride, out_off, count);
+    LB_CUDA(cudaGetLastError());
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int luxb200_rns_plan_create(uint32_t N, uint32_t sizeQ, const uint64_t* q, uint32_t sizeP, const uint64_t* p, int device,
+                            luxb200_rns_plan** out) {
+    if (!q || !p || !out || sizeQ == 0 || sizeP == 0) return lb_fail(LUXB200_ERR_INVALID_ARG, "null argument");
+    *out = nullptr;
+    if (sizeQ > 64 || sizeP > 64) return lb_fail(LUXB200_ERR_UNSUPPORTED, "at most 64 limbs per basis");
+    for (uint32_t i = 0; i < sizeQ + sizeP; ++i) {
+        const uint64_t m = i < sizeQ ? q[i] : p[i - sizeQ];
+        if (m >= (1ull << 62) || !lb::is_prime(m)) return lb_fail(LUXB200_ERR_INVALID_ARG, "moduli must be primes below 2^62");
+        for (uint32_t k = 0; k < i; ++k)
+            if ((k < sizeQ ? q[k] : p[k - sizeQ]) == m) return lb_fail(LUXB200_ERR_INVALID_ARG, "moduli must be pairwise distinct");
+    }
+    LB_TRY(lb_set_device(device));
+    auto* pl = new luxb200_rns_plan();
+    pl->N = N; pl->sizeQ = sizeQ; pl->sizeP = sizeP; pl->device = device;
+    make_tables(q, sizeQ, p, sizeP, pl->up);
+    make_tables(p, sizeP, q, sizeQ, pl->down);
+    pl->pinv.resize(sizeQ); pl->pinv_s.resize(sizeQ);
+    for (uint32_t i = 0; i < sizeQ; ++i) {
+        uint64_t P = 1;
+        for (uint32_t j = 0; j < sizeP; ++j) P = lb::mulmod(P, p[j] % q[i], q[i]);
+        pl->pinv[i] = lb::invmod_prime(P, q[i]);
+        pl->pinv_s[i] = lb::shoup64(pl->pinv[i], q[i]);
+    }
+    int rc = upload_tables(pl->up, pl->dev_up, pl->d_up, N);
+    if (!rc) rc = upload_tables(pl->down, pl->dev_down, pl->d_down, N);
+    if (!rc) {
+        std::vector<u64> flat(q, q + sizeQ);
+        flat.insert(flat.end(), pl->pinv.begin(), pl->pinv.end());
+        flat.insert(flat.end(), pl->pinv_s.begin(), pl->pinv_s.end());
+        rc = pl->dev_tail.ensure(flat.size() * 8);
+        if (!rc && cudaMemcpy(pl->dev_tail.p, flat.data(), flat.size() * 8, cudaMemcpyHostToDevice) != cudaSuccess)
+            rc = lb_fail(LUXB200_ERR_CUDA, "table upload failed");
+        pl->d_q = pl->dev_tail.as<u64>(); pl->d_pinv = pl->d_q + sizeQ; pl->d_pinv_s = pl->d_pinv + sizeQ;
+    }
+    // the NTTs between the steps: only when N is a transform size (the raw basis switch works for any N)
+    bool ntt_ok = N >= 256 && N <= 131072 && !(N & (N - 1));
+    for (uint32_t i = 0; i < sizeQ + sizeP && ntt_ok; ++i) ntt_ok = ((i < sizeQ ? q[i] : p[i - sizeQ]) - 1) % (2ull * N) == 0;
+    if (!rc && ntt_ok) {
+        rc = luxb200_ntt_plan_create(N, sizeQ, q, nullptr, device, &pl->nttQ);
+        if (!rc) rc = luxb200_ntt_plan_create(N, sizeP, p, nullptr, device, &pl->nttP);
+    }
+    if (!rc && cudaStreamCreateWithFlags(&pl->stream, cudaStreamNonBlocking) != cudaSuccess) rc = lb_fail(LUXB200_ERR_CUDA, "stream creation failed");
+    if (rc) { luxb200_rns_plan_destroy(pl); return rc; }
+    *out = pl;
+    return 0;
+}
+
+void luxb200_rns_plan_destroy(luxb200_rns_plan* pl) {
+    if (!pl) return;
+    cudaSetDevice(pl->device);
+    if (pl->nttQ) luxb200_ntt_plan_destroy(pl->nttQ);
+    if (pl->nttP) luxb200_ntt_plan_destroy(pl->nttP);
+    if (pl->stream) cudaStreamDestroy(pl->stream);
+    delete pl;
+}
+
+// DCRTPolyImpl::ApproxSwitchCRTBasis: x [count][sizeQ][N] (COEFFICIENT format, residues mod q_i) -> out [count][sizeP][N];
+// direction 0: Q -> P, 1: P -> Q (then x has sizeP limbs and out sizeQ).  Host buffers.
+int luxb200_approx_switch_crt_basis(luxb200_rns_plan* pl, const uint64_t* x, uint64_t* out, uint64_t count, int direction) {
+    if (!pl || !x || !out) return lb_fail(LUXB200_ERR_INVALID_ARG, "null argument");
+    if (count == 0) return 0;
+    LB_TRY(lb_set_device(pl->device));
+    const RnsDev& D = direction ? pl->d_down : pl->d_up;
+    const uint64_t in_el = (uint64_t)D.sizeQ * pl->N, out_el = (uint64_t)D.sizeP * pl->N;
+    const uint64_t chunk = std::max<uint64_t>(1, (256ull << 20) / ((in_el + out_el) * 8));
+    for (uint64_t off = 0; off < count; off += chunk) {
+        const uint64_t m = std::min(chunk, count - off);
+        LB_TRY(pl->stage_in.ensure(m * in_el * 8)); LB_TRY(pl->stage_out.ensure(m * out_el * 8));
+        LB_CUDA(cudaMemcpyAsync(pl->stage_in.p, x + off * in_el, m * in_el * 8, cudaMemcpyHostToDevice, pl->stream));
+        LB_TRY(launch_switch(pl, D, pl->stage_in.as<u64>(), D.sizeQ, 0, pl->stage_out.as<u64>(), D.sizeP, 0, m));
+        LB_CUDA(cudaMemcpyAsync(out + off * out_el, pl->stage_out.p, m * out_el * 8, cudaMemcpyDeviceToHost, pl->stream));
+        LB_CUDA(cudaStreamSynchronize(pl->stream));
+    }
+    return 0;
+}
+
+// Device-resident composites, EVALUATION format in and out (data on the plan's device, asynchronous on the plan's stream order:
+// each step is followed by a stream synchronisation because the NTT plans own their streams).
+// ApproxModUp: x [count][sizeQ][N] -> out [count][sizeQ + sizeP][N] = the Q limbs unchanged, then the P limbs.
+int luxb200_approx_mod_up_dev(luxb200_rns_plan* pl, const void* x_dev, void* out_dev, uint64_t count) {
+    if (!pl || !x_dev || !out_dev) return lb_fail(LUXB200_ERR_INVALID_ARG, "null argument");
+    if (!pl->nttQ) return lb_fail(LUXB200_ERR_UNSUPPORTED, "this plan has no NTT (N or the moduli do not admit one)");
+    if (count == 0) return 0;
+    LB_TRY(lb_set_device(pl->device));
+    const uint32_t N = pl->N, sq = pl->sizeQ, sp = pl->sizeP;
+    const u64* x = reinterpret_cast<const u64*>(x_dev);
+    u64* out = reinterpret_cast<u64*>(out_dev);
+    LB_TRY(pl->tmpQ.ensure(count * sq * N * 8)); LB_TRY(pl->tmpP.ensure(count * sp * N * 8));
+    rns_copy_limbs_kernel<<<nblk(count * sq * N, 256), 256, 0, pl->stream>>>(x, sq, 0, pl->tmpQ.as<u64>(), sq, 0, sq, N, count);
+    rns_copy_limbs_kernel<<<nblk(count * sq * N, 256), 256, 0, pl->stream>>>(x, sq, 0, out, sq + sp, 0, sq, N, count);
+    LB_CUDA(cudaStreamSynchronize(pl->stream));
+    LB_TRY(luxb200_ntt_batch_dev(pl->nttQ, pl->tmpQ.p, count, 1, 8));          // SetFormat(COEFFICIENT)
+    LB_TRY(luxb200_ntt_plan_sync(pl->nttQ));
+    LB_TRY(launch_switch(pl, pl->d_up, pl->tmpQ.as<u64>(), sq, 0, pl->tmpP.as<u64>(), sp, 0, count));
+    LB_CUDA(cudaStreamSynchronize(pl->stream));
+    LB_TRY(luxb200_ntt_batch_dev(pl->nttP, pl->tmpP.p, count, 0, 8));          // the new limbs to EVALUATION
+    LB_TRY(luxb200_ntt_plan_sync(pl->nttP));
+    rns_copy_limbs_kernel<<<nblk(count * sp * N, 256), 256, 0, pl->stream>>>(pl->tmpP.as<u64>(), sp, 0, out, sq + sp, sq, sp, N, count);
+    LB_CUDA(cudaStreamSynchronize(pl->stream));
+    return 0;
+}
+
+// ApproxModDown (t = 0): x [count][sizeQ + sizeP][N] EVALUATION -> out [count][sizeQ][N] EVALUATION
+int luxb200_approx_mod_down_dev(luxb200_rns_plan* pl, const void* x_dev, void* out_dev, uint64_t count) {
+    if (!pl || !x_dev || !out_dev) return lb_fail(LUXB200_ERR_INVALID_ARG, "null argument");
+    if (!pl->nttQ) return lb_fail(LUXB200_ERR_UNSUPPORTED, "this plan has no NTT (N or the moduli do not admit one)");
+    if (count == 0) return 0;
+    LB_TRY(lb_set_device(pl->device));
+    const uint32_t N = pl->N, sq = pl->sizeQ, sp = pl->sizeP;
+    const u64* x = reinterpret_cast<const u64*>(x_dev);
+    u64* out = reinterpret_cast<u64*>(out_dev);
+    LB_TRY(pl->tmpQ.ensure(count * sq * N * 8)); LB_TRY(pl->tmpP.ensure(count * sp * N * 8));
+    rns_copy_limbs_kernel<<<nblk(count * sp * N, 256), 256, 0, pl->stream>>>(x, sq + sp, sq, pl->tmpP.as<u64>(), sp, 0, sp, N, count);
+    LB_CUDA(cudaStreamSynchronize(pl->stream));
+    LB_TRY(luxb200_ntt_batch_dev(pl->nttP, pl->tmpP.p, count, 1, 8));
+    LB_TRY(luxb200_ntt_plan_sync(pl->nttP));
+    LB_TRY(launch_switch(pl, pl->d_down, pl->tmpP.as<u64>(), sp, 0, pl->tmpQ.as<u64>(), sq, 0, count));
+    LB_CUDA(cudaStreamSynchronize(pl->stream));
+    LB_TRY(luxb200_ntt_batch_dev(pl->nttQ, pl->tmpQ.p, count, 0, 8));
+    LB_TRY(luxb200_ntt_plan_sync(pl->nttQ));
+    rns_moddown_tail_kernel<<<nblk(count * sq * N, 256), 256, 0, pl->stream>>>(x, sq + sp, pl->tmpQ.as<u64>(), out, pl->d_q, pl->d_pinv,
+                                                                             pl->d_pinv_s, sq, N, count);
+    LB_CUDA(cudaGetLastError());
+    LB_CUDA(cudaStreamSynchronize(pl->stream));
+    return 0;
+}
+
+// host-buffer wrappers of the two composites (what = 0 mod up, 1 mod down)
+int luxb200_approx_mod_switch(luxb200_rns_plan* pl, const uint64_t* x, uint64_t* out, uint64_t count, int what) {
+    if (!pl || !x || !out) return lb_fail(LUXB200_ERR_INVALID_ARG, "null argument");
+    if (count == 0) return 0;
+    LB_TRY(lb_set_device(pl->device));
+    const uint64_t limbs_in = what ? pl->sizeQ + pl->sizeP : pl->sizeQ, limbs_out = what ? pl->sizeQ : pl->sizeQ + pl->sizeP;
+    const uint64_t in_el = limbs_in * pl->N, out_el = limbs_out * pl->N;
+    const uint64_t chunk = std::max<uint64_t>(1, (256ull << 20) / ((in_el + out_el) * 8));
+    for (uint64_t off = 0; off < count; off += chunk) {
+        const uint64_t m = std::min(chunk, count - off);
+        LB_TRY(pl->stage_in.ensure(m * in_el * 8)); LB_TRY(pl->stage_out.ensure(m * out_el * 8));
+        LB_CUDA(cudaMemcpy(pl->stage_in.p, x + off * in_el, m * in_el * 8, cudaMemcpyHostToDevice));
+        if (what) LB_TRY(luxb200_approx_mod_down_dev(pl, pl->stage_in.p, pl->stage_out.p, m));
+        else LB_TRY(luxb200_approx_mod_up_dev(pl, pl->stage_in.p, pl->stage_out.p, m));
+        LB_CUDA(cudaMemcpy(out + off * out_el, pl->stage_out.p, m * out_el * 8, cudaMemcpyDeviceToHost));
+    }
+    return 0;
+}
+
+}  // extern "C"

@@ -74,6 +74,12 @@ SIGNATURES = {
     "luxb200_ntt_batch_dev": (INT, [VP, VP, U64, INT, INT]),
     "luxb200_ntt_plan_sync": (INT, [VP]),
     "luxb200_ntt_last_ms": (C.c_float, [VP]),
+    "luxb200_rns_plan_create": (INT, [U32, U32, VP, U32, VP, INT, C.POINTER(VP)]),
+    "luxb200_rns_plan_destroy": (None, [VP]),
+    "luxb200_approx_switch_crt_basis": (INT, [VP, VP, VP, U64, INT]),
+    "luxb200_approx_mod_switch": (INT, [VP, VP, VP, U64, INT]),
+    "luxb200_approx_mod_up_dev": (INT, [VP, VP, VP, U64]),
+    "luxb200_approx_mod_down_dev": (INT, [VP, VP, VP, U64]),
     "luxb200_evalbingate_batch_dev": (INT, [VP, INT, VP, VP, VP, VP, VP, VP, U64]),
     "luxb200_circuit_batch": (INT, [VP, U32, VP, U32, VP, U32, VP, VP, VP, VP, U64]),
     "luxb200_circuit_batch_ex": (INT, [VP, U32, VP, U32, VP, U32, VP, U32, U64, VP, VP, VP, VP, U64]),

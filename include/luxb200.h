@@ -184,6 +184,26 @@ int luxb200_ntt_plan_sync(luxb200_ntt_plan* plan);
 float luxb200_ntt_last_ms(luxb200_ntt_plan* plan);   /* CUDA-event time of the last *_dev call's kernels */
 #define luxb200_dcrt_ntt_batch luxb200_ntt_batch     /* DCRTPoly::SwitchFormat = the L > 1 case */
 
+/* ---- RNS basis conversion around the DCRT NTT (CKKS / BGV hybrid key switching) ---------------------------------------
+ *   luxb200_approx_switch_crt_basis  DCRTPolyImpl::ApproxSwitchCRTBasis  src/core/include/lattice/hal/default/dcrtpoly-impl.h:910-957
+ *   luxb200_approx_mod_switch what=0 DCRTPolyImpl::ApproxModUp           :960-986  (KeySwitchHYBRID::EvalKeySwitchPrecomputeCore,
+ *                                                                         src/pke/lib/keyswitch/keyswitch-hybrid.cpp:328-412)
+ *                             what=1 DCRTPolyImpl::ApproxModDown (t = 0) :988-1030 (EvalFastKeySwitchCore, :414-436)
+ * A plan holds two bases Q = {q_i} and P = {p_j} (pairwise distinct primes below 2^62) and the tables derived from them
+ * ((Q/q_i)^-1 mod q_i, (Q/q_i) mod p_j, P^-1 mod q_i, and the same with the roles swapped).  Data [count][limbs][N] uint64,
+ * one canonical residue per element. */
+typedef struct luxb200_rns_plan luxb200_rns_plan;
+int luxb200_rns_plan_create(uint32_t N, uint32_t sizeQ, const uint64_t* q, uint32_t sizeP, const uint64_t* p, int device,
+                            luxb200_rns_plan** out);
+void luxb200_rns_plan_destroy(luxb200_rns_plan* plan);
+/* COEFFICIENT-format limbs; direction 0: x over Q -> out over P, 1: x over P -> out over Q.  Host buffers. */
+int luxb200_approx_switch_crt_basis(luxb200_rns_plan* plan, const uint64_t* x, uint64_t* out, uint64_t count, int direction);
+/* EVALUATION format in and out; what = 0: x [count][sizeQ][N] -> out [count][sizeQ+sizeP][N] (Q limbs, then P limbs);
+ * what = 1: x [count][sizeQ+sizeP][N] -> out [count][sizeQ][N].  Host buffers; the _dev variants take device pointers. */
+int luxb200_approx_mod_switch(luxb200_rns_plan* plan, const uint64_t* x, uint64_t* out, uint64_t count, int what);
+int luxb200_approx_mod_up_dev(luxb200_rns_plan* plan, const void* x_dev, void* out_dev, uint64_t count);
+int luxb200_approx_mod_down_dev(luxb200_rns_plan* plan, const void* x_dev, void* out_dev, uint64_t count);
+
 /* ---- device-resident batched gates (inputs already in HBM as uint32) ---------------------------------- */
 /* a1,a2 [count][n] u32, b1,b2 [count] u32 on ctx's device; out oa [count][n] u32, ob [count] u32. Asynchronous on the
  * context stream; call luxb200_synchronize before reading. */

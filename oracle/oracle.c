@@ -886,6 +886,75 @@ int orc_evalsign_decomp(OrcCtx** cs, int ncs, const u64* a, const u64* b, u64* o
     return rc;
 }
 
+/* ---- RNS basis conversion: DCRTPolyImpl::ApproxSwitchCRTBasis / ApproxModUp / ApproxModDown (dcrtpoly-impl.h:910-1030) ----- */
+static u64 prod_mod_except(const u64* m, u32 cnt, u32 skip, u64 mod) {
+    u64 r = 1 % mod;
+    for (u32 k = 0; k < cnt; ++k) if (k != skip) r = mulmod(r, m[k] % mod, mod);
+    return r;
+}
+/* x [count][sizeQ][N] residues mod q_i (COEFFICIENT) -> out [count][sizeP][N]: out_j = sum_i [x_i (Q/q_i)^-1]_{q_i} (Q/q_i) mod p_j;
+ * the reference sums the 128-bit products and reduces once (:921-936) — the same integer, reduced term by term here */
+int orc_approx_switch_crt_basis(u32 N, u32 sizeQ, const u64* q, u32 sizeP, const u64* p, const u64* x, u64* out, u64 count) {
+    u64* hinv = malloc(sizeof(u64) * sizeQ);
+    u64* hat = malloc(sizeof(u64) * sizeQ * sizeP);
+    for (u32 i = 0; i < sizeQ; ++i) {
+        hinv[i] = invmod(prod_mod_except(q, sizeQ, i, q[i]), q[i]);
+        for (u32 j = 0; j < sizeP; ++j) hat[i * sizeP + j] = prod_mod_except(q, sizeQ, i, p[j]);
+    }
+#pragma omp parallel for
+    for (u64 c = 0; c < count; ++c)
+        for (u32 k = 0; k < N; ++k)
+            for (u32 j = 0; j < sizeP; ++j) {
+                u64 s = 0;
+                for (u32 i = 0; i < sizeQ; ++i) {
+                    u64 xh = mulmod(x[(c * sizeQ + i) * N + k], hinv[i], q[i]);
+                    s = addmod(s, mulmod(xh % p[j], hat[i * sizeP + j], p[j]), p[j]);
+                }
+                out[(c * sizeP + j) * N + k] = s;
+            }
+    free(hinv); free(hat);
+    return 0;
+}
+/* ApproxModUp (:960-986): EVALUATION x over Q -> Q limbs unchanged, then the P limbs (INTT, basis switch, NTT) */
+int orc_approx_mod_up(u32 N, u32 sizeQ, const u64* q, u32 sizeP, const u64* p, const u64* x, u64* out, u64 count) {
+    u64* t = malloc(sizeof(u64) * count * sizeQ * N);
+    u64* s = malloc(sizeof(u64) * count * sizeP * N);
+    memcpy(t, x, sizeof(u64) * count * sizeQ * N);
+    for (u64 c = 0; c < count; ++c)
+        for (u32 i = 0; i < sizeQ; ++i) orc_ntt(q[i], orc_root_of_unity(2 * (u64)N, q[i]), N, t + (c * sizeQ + i) * N, 1, 1, 1);
+    orc_approx_switch_crt_basis(N, sizeQ, q, sizeP, p, t, s, count);
+    for (u64 c = 0; c < count; ++c) {
+        for (u32 j = 0; j < sizeP; ++j) orc_ntt(p[j], orc_root_of_unity(2 * (u64)N, p[j]), N, s + (c * sizeP + j) * N, 1, 0, 1);
+        memcpy(out + c * (sizeQ + sizeP) * N, x + c * sizeQ * N, sizeof(u64) * sizeQ * N);
+        memcpy(out + (c * (sizeQ + sizeP) + sizeQ) * N, s + c * sizeP * N, sizeof(u64) * sizeP * N);
+    }
+    free(t); free(s);
+    return 0;
+}
+/* ApproxModDown with t = 0 (:988-1030): EVALUATION x over Q u P -> (x_i - Switch_{P->Q}(x_P)_i) P^-1 mod q_i */
+int orc_approx_mod_down(u32 N, u32 sizeQ, const u64* q, u32 sizeP, const u64* p, const u64* x, u64* out, u64 count) {
+    u64* t = malloc(sizeof(u64) * count * sizeP * N);
+    u64* s = malloc(sizeof(u64) * count * sizeQ * N);
+    for (u64 c = 0; c < count; ++c)
+        for (u32 j = 0; j < sizeP; ++j) {
+            memcpy(t + (c * sizeP + j) * N, x + (c * (sizeQ + sizeP) + sizeQ + j) * N, sizeof(u64) * N);
+            orc_ntt(p[j], orc_root_of_unity(2 * (u64)N, p[j]), N, t + (c * sizeP + j) * N, 1, 1, 1);
+        }
+    orc_approx_switch_crt_basis(N, sizeP, p, sizeQ, q, t, s, count);
+    for (u64 c = 0; c < count; ++c)
+        for (u32 i = 0; i < sizeQ; ++i) {
+            u64* si = s + (c * sizeQ + i) * N;
+            orc_ntt(q[i], orc_root_of_unity(2 * (u64)N, q[i]), N, si, 1, 0, 1);
+            u64 pinv = 1;
+            for (u32 j = 0; j < sizeP; ++j) pinv = mulmod(pinv, p[j] % q[i], q[i]);
+            pinv = invmod(pinv, q[i]);
+            for (u32 k = 0; k < N; ++k)
+                out[(c * sizeQ + i) * N + k] = mulmod(submod(x[(c * (sizeQ + sizeP) + i) * N + k], si[k], q[i]), pinv, q[i]);
+        }
+    free(t); free(s);
+    return 0;
+}
+
 double orc_time_bingate(OrcCtx* c, int gate, const u64* a1, const u64* b1, const u64* a2, const u64* b2, u64* oa,
                         u64* ob, u64 count, int threads) {
     struct timespec t0, t1;

@@ -76,6 +76,13 @@ int orc_evalfloor(OrcCtx*, const uint64_t* a, const uint64_t* b, uint64_t* oa, u
 uint32_t orc_evaldecomp_count(uint64_t q, uint64_t mod, uint64_t beta);
 int orc_evalsign_decomp(OrcCtx** cs, int ncs, const uint64_t* a, const uint64_t* b, uint64_t* oa, uint64_t* ob,
                         uint64_t* out_mod, uint64_t count, uint64_t mod, uint64_t beta, int what, int threads);
+/* RNS basis conversion (dcrtpoly-impl.h:910-1030); data [count][limbs][N] */
+int orc_approx_switch_crt_basis(uint32_t N, uint32_t sizeQ, const uint64_t* q, uint32_t sizeP, const uint64_t* p,
+                                const uint64_t* x, uint64_t* out, uint64_t count);
+int orc_approx_mod_up(uint32_t N, uint32_t sizeQ, const uint64_t* q, uint32_t sizeP, const uint64_t* p, const uint64_t* x,
+                      uint64_t* out, uint64_t count);
+int orc_approx_mod_down(uint32_t N, uint32_t sizeQ, const uint64_t* q, uint32_t sizeP, const uint64_t* p, const uint64_t* x,
+                        uint64_t* out, uint64_t count);
 double orc_time_bingate(OrcCtx*, int gate, const uint64_t* a1, const uint64_t* b1, const uint64_t* a2,
                         const uint64_t* b2, uint64_t* oa, uint64_t* ob, uint64_t count, int threads);
 int orc_max_threads(void);

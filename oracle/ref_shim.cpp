@@ -561,6 +561,88 @@ int ref_evaldecomp(void* hv, const uint64_t* a, const uint64_t* b, uint64_t* out
     return k;
 }
 
+
+// ---- RNS basis conversion (CKKS/BGV hybrid key switching): the reference's own DCRTPoly methods --------------------------
+// ApproxSwitchCRTBasis / ApproxModUp / ApproxModDown (dcrtpoly-impl.h:910-1030) with the tables CryptoParametersRNS::
+// PrecomputeCRTTables (src/pke/lib/schemerns/rns-cryptoparameters.cpp) would hand them, computed here from their textbook
+// definitions with BigInteger: QHat_i = Q / q_i, QHatInvModq_i = QHat_i^-1 mod q_i, QHatModp[i][j] = QHat_i mod p_j,
+// modpBarrettMu_j = floor(2^128 / p_j), PInvModq_i = P^-1 mod q_i.
+namespace {
+struct RnsTables {
+    std::vector<NativeInteger> hatInv, hatInvPrecon;
+    std::vector<std::vector<NativeInteger>> hatMod;
+    std::vector<DoubleNativeInt> mu;
+};
+RnsTables rns_tables(const std::vector<NativeInteger>& from, const std::vector<NativeInteger>& to) {
+    RnsTables T;
+    BigInteger Q(1);
+    for (auto& m : from) Q *= BigInteger(m.ConvertToInt<uint64_t>());
+    for (size_t i = 0; i < from.size(); ++i) {
+        BigInteger qi(from[i].ConvertToInt<uint64_t>());
+        BigInteger hat = Q / qi;
+        NativeInteger inv = NativeInteger(hat.Mod(qi).ConvertToInt<uint64_t>()).ModInverse(from[i]);
+        T.hatInv.push_back(inv);
+        T.hatInvPrecon.push_back(inv.PrepModMulConst(from[i]));
+        std::vector<NativeInteger> row;
+        for (auto& pj : to) row.push_back(NativeInteger(hat.Mod(BigInteger(pj.ConvertToInt<uint64_t>())).ConvertToInt<uint64_t>()));
+        T.hatMod.push_back(row);
+    }
+    for (auto& pj : to) {
+        const DoubleNativeInt all = ~DoubleNativeInt(0);   // floor(2^128 / p) = floor((2^128 - 1) / p) for p not a power of two
+        T.mu.push_back(all / DoubleNativeInt(pj.ConvertToInt<uint64_t>()));
+    }
+    return T;
+}
+}  // namespace
+
+// x [count][limbs_in][N] -> out [count][limbs_out][N].  what 0: ApproxSwitchCRTBasis Q -> P on COEFFICIENT data (sizeQ in,
+// sizeP out); 1: ApproxModUp, EVALUATION (sizeQ in, sizeQ + sizeP out); 2: ApproxModDown with t = 0, EVALUATION (sizeQ + sizeP
+// in, sizeQ out)
+int ref_rns_op(uint32_t N, uint32_t sizeQ, const uint64_t* q, uint32_t sizeP, const uint64_t* p, const uint64_t* x, uint64_t* out,
+               uint64_t count, int what) {
+    try {
+        std::vector<NativeInteger> mq, mp, rq, rp, mqp, rqp;
+        for (uint32_t i = 0; i < sizeQ; ++i) { mq.emplace_back(q[i]); rq.push_back(RootOfUnity<NativeInteger>(2 * N, mq.back())); }
+        for (uint32_t j = 0; j < sizeP; ++j) { mp.emplace_back(p[j]); rp.push_back(RootOfUnity<NativeInteger>(2 * N, mp.back())); }
+        mqp = mq; mqp.insert(mqp.end(), mp.begin(), mp.end());
+        rqp = rq; rqp.insert(rqp.end(), rp.begin(), rp.end());
+        auto paramsQ  = std::make_shared<ILDCRTParams<BigInteger>>(2 * N, mq, rq);
+        auto paramsP  = std::make_shared<ILDCRTParams<BigInteger>>(2 * N, mp, rp);
+        auto paramsQP = std::make_shared<ILDCRTParams<BigInteger>>(2 * N, mqp, rqp);
+        const RnsTables up = rns_tables(mq, mp), down = rns_tables(mp, mq);
+        std::vector<NativeInteger> pInv, pInvPrecon;
+        BigInteger P(1);
+        for (auto& m : mp) P *= BigInteger(m.ConvertToInt<uint64_t>());
+        for (auto& qi : mq) {
+            NativeInteger inv = NativeInteger(P.Mod(BigInteger(qi.ConvertToInt<uint64_t>())).ConvertToInt<uint64_t>()).ModInverse(qi);
+            pInv.push_back(inv);
+            pInvPrecon.push_back(inv.PrepModMulConst(qi));
+        }
+        const uint32_t lin = what == 2 ? sizeQ + sizeP : sizeQ, lout = what == 0 ? sizeP : (what == 1 ? sizeQ + sizeP : sizeQ);
+        for (uint64_t c = 0; c < count; ++c) {
+            DCRTPoly in(what == 2 ? paramsQP : paramsQ, what == 0 ? Format::COEFFICIENT : Format::EVALUATION, true);
+            for (uint32_t l = 0; l < lin; ++l) {
+                NativePoly& limb = in.GetAllElements()[l];
+                for (uint32_t k = 0; k < N; ++k) limb[k] = NativeInteger(x[(c * lin + l) * N + k]);
+            }
+            DCRTPoly res;
+            if (what == 0) res = in.ApproxSwitchCRTBasis(paramsQ, paramsP, up.hatInv, up.hatInvPrecon, up.hatMod, up.mu);
+            else if (what == 1) { in.ApproxModUp(paramsQ, paramsP, paramsQP, up.hatInv, up.hatInvPrecon, up.hatMod, up.mu); res = in; }
+            else res = in.ApproxModDown(paramsQ, paramsP, pInv, pInvPrecon, down.hatInv, down.hatInvPrecon, down.hatMod, down.mu, {}, {},
+                                        NativeInteger(0), {});
+            if (res.GetNumOfElements() != lout) return -2;
+            for (uint32_t l = 0; l < lout; ++l) {
+                const NativePoly& limb = res.GetAllElements()[l];
+                for (uint32_t k = 0; k < N; ++k) out[(c * lout + l) * N + k] = limb[k].ConvertToInt<uint64_t>();
+            }
+        }
+        return 0;
+    }
+    catch (...) {
+        return -1;
+    }
+}
+
 // ---- CPU baseline timers (bench.py --impl reference / cpu_baseline) --------------------------------
 // `count` EvalBinGate(gate) on count ciphertext pairs, outer OMP loop over independent gates — the shape
 // of EvalBinGateBatch (src/binfhe/lib/batch/batch.cpp:197-200). Returns seconds.

@@ -664,3 +664,33 @@ def test_device_btkeygen(name, method):
     bsk3, _, _ = ctx2.ExportKeys()
     assert not (bsk3 == bsk).all()
     ctx.close(); ctx2.close(); oc.close()
+
+
+# ---- RNS basis conversion around the DCRT NTT (CKKS / BGV hybrid key switching) ---------------------------
+@pytest.mark.parametrize("N,sizeQ,sizeP,bits,cnt", [(1024, 3, 2, 50, 3), (4096, 4, 5, 60, 2), (65536, 8, 3, 60, 1), (16384, 1, 4, 55, 2),
+                                                    (65536, 3, 30, 60, 1)])
+def test_rns_basis_conversion_vs_oracle(N, sizeQ, sizeP, bits, cnt):
+    """luxb200_approx_switch_crt_basis / approx_mod_switch = DCRTPolyImpl::ApproxSwitchCRTBasis / ApproxModUp / ApproxModDown
+    (dcrtpoly-impl.h:910-1030), every residue against the oracle (pinned to the reference's DCRTPoly methods on the CPU).
+    (65536, 3, 30): one digit of 3 limbs raised to a 33-limb basis, the EvalKeySwitchPrecomputeCore shape of configs[4]."""
+    from fhe_b200.context import RNSPlan
+    O = oracle()
+    chain = np.zeros(sizeQ + sizeP, np.uint64); psi = chain.copy()
+    O.orc_dcrt_chain(N, sizeQ + sizeP, bits, P(chain), P(psi))
+    q, p = np.ascontiguousarray(chain[:sizeQ]), np.ascontiguousarray(chain[sizeQ:])
+    rng = np.random.default_rng(N + sizeQ + sizeP)
+    x = np.stack([np.stack([rng.integers(0, int(m), size=N, dtype=np.uint64) for m in q]) for _ in range(cnt)])
+    x[0, 0, :] = q[0] - np.uint64(1)
+    x[-1, -1, :] = 0
+    xqp = np.stack([np.stack([rng.integers(0, int(m), size=N, dtype=np.uint64) for m in chain]) for _ in range(cnt)])
+    pl = RNSPlan(N, q, p)
+    ref = np.zeros((cnt, sizeP, N), np.uint64)
+    O.orc_approx_switch_crt_basis(N, sizeQ, P(q), sizeP, P(p), P(x), P(ref), cnt)
+    assert (pl.ApproxSwitchCRTBasis(x, 0) == ref).all()
+    ref = np.zeros((cnt, sizeQ + sizeP, N), np.uint64)
+    O.orc_approx_mod_up(N, sizeQ, P(q), sizeP, P(p), P(x), P(ref), cnt)
+    assert (pl.ApproxModUp(x) == ref).all()
+    ref = np.zeros((cnt, sizeQ, N), np.uint64)
+    O.orc_approx_mod_down(N, sizeQ, P(q), sizeP, P(p), P(xqp), P(ref), cnt)
+    assert (pl.ApproxModDown(xqp) == ref).all()
+    pl.close()

@@ -173,3 +173,24 @@ def test_largeprec_floor_sign_decomp_pin_the_oracle(logQ, time_opt):
     rc.close()
     for oc in ocs:
         oc.close()
+
+
+@pytest.mark.parametrize("N,sizeQ,sizeP,bits", [(1024, 3, 2, 50), (4096, 4, 5, 60), (2048, 1, 3, 45)])
+def test_rns_basis_conversion_pins_the_oracle(N, sizeQ, sizeP, bits):
+    """DCRTPolyImpl::ApproxSwitchCRTBasis / ApproxModUp / ApproxModDown (dcrtpoly-impl.h:910-1030) of the real reference, fed
+    the tables of CryptoParametersRNS::PrecomputeCRTTables, against the oracle's restatement, every residue."""
+    R, O = orclib.ref(), orclib.oracle()
+    chain = np.zeros(sizeQ + sizeP, np.uint64); psi = chain.copy()
+    O.orc_dcrt_chain(N, sizeQ + sizeP, bits, P(chain), P(psi))
+    q, p = np.ascontiguousarray(chain[:sizeQ]), np.ascontiguousarray(chain[sizeQ:])
+    rng = np.random.default_rng(N + sizeQ)
+    cnt = 2
+    x = np.stack([np.stack([rng.integers(0, int(m), size=N, dtype=np.uint64) for m in q]) for _ in range(cnt)])
+    x[0, 0, :] = q[0] - np.uint64(1)
+    xqp = np.stack([np.stack([rng.integers(0, int(m), size=N, dtype=np.uint64) for m in chain]) for _ in range(cnt)])
+    for what, (inp, lout, fn) in enumerate([(x, sizeP, O.orc_approx_switch_crt_basis), (x, sizeQ + sizeP, O.orc_approx_mod_up),
+                                            (xqp, sizeQ, O.orc_approx_mod_down)]):
+        a = np.zeros((cnt, lout, N), np.uint64); b = a.copy()
+        assert R.ref_rns_op(N, sizeQ, P(q), sizeP, P(p), P(inp), P(a), cnt, what) == 0
+        assert fn(N, sizeQ, P(q), sizeP, P(p), P(inp), P(b), cnt) == 0
+        assert (a == b).all(), what
