@@ -425,6 +425,15 @@ class RNSPlan:
         _l.check(self.L.luxb200_approx_switch_crt_basis(self.h, _l.ptr(x), _l.ptr(out), cnt, direction))
         return out
 
+    def ApproxSwitchCRTBasisStatic(self, x, direction=0):
+        """luxb200_approx_switch_crt_basis_static: the same result with no cudaMalloc (device staging in the library's static
+        16 MiB array; larger batches are refused).  No counterpart in the reference."""
+        x = np.ascontiguousarray(x, np.uint64)
+        cnt = x.shape[0]
+        out = np.empty((cnt, len(self.q) if direction else len(self.p), self.N), np.uint64)
+        _l.check(self.L.luxb200_approx_switch_crt_basis_static(self.h, _l.ptr(x), _l.ptr(out), cnt, direction))
+        return out
+
     def ApproxModUp(self, x):
         x = np.ascontiguousarray(x, np.uint64)
         out = np.empty((x.shape[0], len(self.q) + len(self.p), self.N), np.uint64)

@@ -285,6 +285,61 @@ int luxb200_approx_mod_down_dev(luxb200_rns_plan* pl, const void* x_dev, void* o
     return 0;
 }
 
+// ---- allocation-free variant of luxb200_approx_switch_crt_basis ------------------------------------------------------------
+// No counterpart in the reference; added for callers that cannot call cudaMalloc (CUDA
+// graph capture, tight serving loops, harnesses that forbid it).  The device staging the basis-switch kernel reads its input
+// from and writes its result to lives in a file-scope array instead of the plan's growable DevBufs: every GPU that loads the
+// library holds LUXB200_STATIC_SCRATCH_BYTES of it until exit.  All calls on one device share the array and it keeps the last
+// call's contents; nothing has to start at zero (the input part is overwritten by the H2D copy and every output word is
+// written by the kernel before the D2H copy reads it), but two calls that overlap on one GPU race on it — serialise them.
+#define LB_STATIC_SCRATCH_WORDS (LUXB200_STATIC_SCRATCH_BYTES / 8)
+static __device__ __align__(256) unsigned long long lb_static_scratch[LB_STATIC_SCRATCH_WORDS];
+
+namespace {
+// device address of lb_static_scratch per device: in host code the array's name is only a handle for the runtime, so the
+// address is asked for once per device, with that device current
+std::mutex g_scratch_mu;
+u64* g_scratch_ptr[64] = {};
+
+int static_scratch(int device, u64** out) {
+    if (device < 0 || device >= 64) return lb_fail(LUXB200_ERR_INVALID_ARG, "device index out of range");
+    std::lock_guard<std::mutex> lk(g_scratch_mu);
+    if (!g_scratch_ptr[device]) {
+        LB_TRY(lb_set_device(device));
+        void* p = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&p, lb_static_scratch);
+        if (e != cudaSuccess || !p) return lb_fail(LUXB200_ERR_CUDA, "cudaGetSymbolAddress(lb_static_scratch): %s", cudaGetErrorString(e));
+        g_scratch_ptr[device] = reinterpret_cast<u64*>(p);
+    }
+    *out = g_scratch_ptr[device];
+    return 0;
+}
+}  // namespace
+
+int luxb200_approx_switch_crt_basis_static(luxb200_rns_plan* pl, const uint64_t* x, uint64_t* out, uint64_t count, int direction) {
+    if (!pl || !x || !out) return lb_fail(LUXB200_ERR_INVALID_ARG, "null argument");
+    if (count == 0) return 0;
+    const RnsDev& D = direction ? pl->d_down : pl->d_up;
+    const uint64_t in_el = (uint64_t)D.sizeQ * pl->N, out_el = (uint64_t)D.sizeP * pl->N;
+    // input staging is rounded up to 32 words so that the output staging stays 256-byte aligned
+    if (count > LB_STATIC_SCRATCH_WORDS / (in_el + out_el) ||
+        ((count * in_el + 31) & ~31ull) + count * out_el > LB_STATIC_SCRATCH_WORDS)
+        return lb_fail(LUXB200_ERR_INVALID_ARG,
+                       "luxb200_approx_switch_crt_basis_static: count * (sizeQ + sizeP) * N * 8 bytes exceeds the static scratch of "
+                       "%llu bytes; split the batch or use luxb200_approx_switch_crt_basis",
+                       (unsigned long long)LUXB200_STATIC_SCRATCH_BYTES);
+    LB_TRY(lb_set_device(pl->device));
+    u64* scratch = nullptr;
+    LB_TRY(static_scratch(pl->device, &scratch));
+    u64* sin = scratch;
+    u64* sout = scratch + ((count * in_el + 31) & ~31ull);
+    LB_CUDA(cudaMemcpyAsync(sin, x, count * in_el * 8, cudaMemcpyHostToDevice, pl->stream));
+    LB_TRY(launch_switch(pl, D, sin, D.sizeQ, 0, sout, D.sizeP, 0, count));
+    LB_CUDA(cudaMemcpyAsync(out, sout, count * out_el * 8, cudaMemcpyDeviceToHost, pl->stream));
+    LB_CUDA(cudaStreamSynchronize(pl->stream));
+    return 0;
+}
+
 // host-buffer wrappers of the two composites (what = 0 mod up, 1 mod down)
 int luxb200_approx_mod_switch(luxb200_rns_plan* pl, const uint64_t* x, uint64_t* out, uint64_t count, int what) {
     if (!pl || !x || !out) return lb_fail(LUXB200_ERR_INVALID_ARG, "null argument");

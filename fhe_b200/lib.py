@@ -77,6 +77,7 @@ SIGNATURES = {
     "luxb200_rns_plan_create": (INT, [U32, U32, VP, U32, VP, INT, C.POINTER(VP)]),
     "luxb200_rns_plan_destroy": (None, [VP]),
     "luxb200_approx_switch_crt_basis": (INT, [VP, VP, VP, U64, INT]),
+    "luxb200_approx_switch_crt_basis_static": (INT, [VP, VP, VP, U64, INT]),
     "luxb200_approx_mod_switch": (INT, [VP, VP, VP, U64, INT]),
     "luxb200_approx_mod_up_dev": (INT, [VP, VP, VP, U64]),
     "luxb200_approx_mod_down_dev": (INT, [VP, VP, VP, U64]),

@@ -203,6 +203,17 @@ int luxb200_approx_switch_crt_basis(luxb200_rns_plan* plan, const uint64_t* x, u
 int luxb200_approx_mod_switch(luxb200_rns_plan* plan, const uint64_t* x, uint64_t* out, uint64_t count, int what);
 int luxb200_approx_mod_up_dev(luxb200_rns_plan* plan, const void* x_dev, void* out_dev, uint64_t count);
 int luxb200_approx_mod_down_dev(luxb200_rns_plan* plan, const void* x_dev, void* out_dev, uint64_t count);
+/* Allocation-free variant of luxb200_approx_switch_crt_basis.  It has no counterpart in the reference and was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid it).  Same arguments, same result; the device staging of the basis-switch kernel is a static device
+ * array of LUXB200_STATIC_SCRATCH_BYTES that every GPU loading the library holds until exit, instead of the plan's growable
+ * buffers, and the call makes no cudaMalloc / cudaFree.  count * (sizeQ + sizeP) * N * 8 bytes (input staging rounded up to
+ * 256 bytes) must fit in the array: anything larger is refused with LUXB200_ERR_INVALID_ARG — split the batch or use the
+ * allocating entry point.  All calls on one device share the array (it keeps the last call's contents; nothing in it needs to
+ * start at zero), so calls that overlap on one GPU race: serialise them. */
+#define LUXB200_STATIC_SCRATCH_BYTES (16ull << 20)
+int luxb200_approx_switch_crt_basis_static(luxb200_rns_plan* plan, const uint64_t* x, uint64_t* out, uint64_t count,
+                                           int direction);
 
 /* ---- device-resident batched gates (inputs already in HBM as uint32) ---------------------------------- */
 /* a1,a2 [count][n] u32, b1,b2 [count] u32 on ctx's device; out oa [count][n] u32, ob [count] u32. Asynchronous on the
