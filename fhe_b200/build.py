@@ -13,7 +13,7 @@ FLAGS = ["-std=c++17", "-O3", "-lineinfo", "-gencode", "arch=compute_100a,code=s
 OBJ = os.path.join(HERE, "_obj")
 # translation units: api.cu holds every kernel of the bootstrapping / NTT path (minutes to compile); circuit.cu is the
 # level scheduler above it
-UNITS = ["api.cu", "circuit.cu", "rns.cu"]
+UNITS = ["api.cu", "br11.cu", "circuit.cu", "rns.cu"]
 
 
 def sources():

@@ -3,6 +3,7 @@
 
 #include "api_common.h"
 #include "aux_kernels.cuh"
+#include "ks_tile.cuh"
 #include "br_sched.cuh"
 #include "br_wide.cuh"
 #include "keygen.cuh"
@@ -168,7 +169,12 @@ int luxb200_ctx_create(const luxb200_params* p, int device, luxb200_ctx** out) {
     if ((u128_t)p->qKS * p->N * c->digitsKS >= ((u128_t)1 << 64)) { luxb200_ctx_destroy(c); return lb_fail(LUXB200_ERR_UNSUPPORTED, "qKS too large for the key-switch accumulator"); }
     // the register-resident warp-pair kernels cover N = 1024 with 2 or 3 digits and N = 512 with 2, Q < 2^30; everything else
     // (N = 2048, 64-bit Q, 1 / 4 / 5 digits) runs the shared-memory kernel of br_wide.cuh
-    const bool fast = p->Q < (1ull << 30) && ((c->logN == 10 && (c->rows == 4 || c->rows == 6)) || (c->logN == 9 && c->rows == 4));
+    // (r2: N = 2048 GINX with 2 digits also fits the register-resident kernel — 64 coefficients per lane, 255 registers, 4
+    // ciphertexts per SM: 1.34x the shared-memory kernel.  Its step body no longer fits the instruction caches (ncu: 2.3
+    // no_instruction stalls per issue), and the scheduled kernel at that size is slower than br_wide.cuh, so AP / LMKCDEY at
+    // N = 2048 stay there.)
+    const bool fast = p->Q < (1ull << 30) && ((c->logN == 10 && (c->rows == 4 || c->rows == 6)) || (c->logN == 9 && c->rows == 4) ||
+                                               (c->logN == 11 && c->rows == 4 && p->Q >= (1ull << 27) && p->method == LUXB200_GINX));
     c->wide.on = !fast;
     if (c->wide.on) {
         luxb200_ctx::Wide& W = c->wide;
@@ -189,9 +195,12 @@ int luxb200_ctx_create(const luxb200_params* p, int device, luxb200_ctx** out) {
         uint32_t b = 0;
         while ((xmax >> b) != 0) ++b;
         uint32_t s = b > 32 ? b - 32 : 0;
-        if (s > bits_of(p->Q) - 1) { luxb200_ctx_destroy(c); return lb_fail(LUXB200_ERR_UNSUPPORTED, "Q too large for the 64->32 reduction (rows=%u)", c->rows); }
+        // mu = floor(2^(s+32) / Q): below 2^32 when 2^s < Q; the N = 2048 kernels (reduce64x) take up to 34 bits
+        const u128_t mu = (((u128_t)1) << (s + 32)) / Q;
+        if ((mu >> 32) != 0 && (c->logN < 11 || (mu >> 34) != 0)) { luxb200_ctx_destroy(c); return lb_fail(LUXB200_ERR_UNSUPPORTED, "Q too large for the 64->32 reduction (rows=%u)", c->rows); }
         c->red_s = s;
-        c->red_mu = (uint32_t)((((u128_t)1) << (s + 32)) / Q);
+        c->red_mu = (uint32_t)mu;
+        c->red_mu_hi = (uint32_t)(mu >> 32);
     }
     rc = c->ntt.build(p->N, p->Q, c->p.psi);
     }

@@ -83,7 +83,7 @@ struct luxb200_ctx {
     uint32_t digitsG = 0, digitsKS = 0, digitsR = 0, rows = 0, logN = 0;
     uint32_t npad = 0;       // padded KSK row length
     uint32_t ks_elem = 0;    // bytes per KSK element (2 or 4)
-    uint32_t red_s = 0, red_mu = 0;
+    uint32_t red_s = 0, red_mu = 0, red_mu_hi = 0;
     cudaStream_t stream = nullptr;
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     Ntt32Tables ntt;
@@ -101,6 +101,7 @@ struct luxb200_ctx {
     DevBuf in0, in1, in2, in3, wa, wb, lut, ext, oa, ob, o64a, o64b, sched, tmpa, tmpb, tmpc, tmpd;
     DevBuf cx1a, cx1b, cx2a, cx2b;   // CMUX intermediates (two NAND results), kept so the call does no cudaMalloc/cudaFree
     DevBuf xin;                      // extended (N, Q) inputs packed [count][N+1] before SwitchCTtoqn
+    DevBuf ksdig;                    // ks_tile.cuh: key-switch digits, coefficient-major [N/2][stride] u32
     DevBuf cpa, cpb, cdesc, clsel;   // gate circuits (circuit.cu): wire pool (a, b), gate descriptors, per-item table offsets
     uint64_t launches = 0;
     float t_prep = 0, t_br = 0, t_ks = 0, t_total = 0;
@@ -118,6 +119,7 @@ struct luxb200_ctx {
 };
 
 int lb_set_device(int device);
+int lb_launch_br11(luxb200_ctx* c, const BrParams& P, int sched_only);   // br11.cu
 int lb_build_wide_tables(luxb200_ctx* c);
 #define LB_LOCK(c) std::lock_guard<std::recursive_mutex> lb_guard_((c)->mu)
 

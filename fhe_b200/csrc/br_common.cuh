@@ -33,7 +33,7 @@ struct BrParams {
     u32 mode;              // 0: lut prologue + extract epilogue, 1: acc_io in/out (raw EvalAcc)
     u32 amul;              // GINX: 2N / ctmod
     u32 auto_off;          // LMKCDEY: u32 offset of the automorphism keys inside bsk
-    u32 pad;
+    u32 red_mu_hi;         // bits 32.. of the reduce64 constant (N = 2048 sets with 29- / 30-bit Q; 0 otherwise)
 };
 
 // sigma: storage position of EVALUATION index p = E*l + r, chosen so that a lane's 4 consecutive
@@ -56,6 +56,13 @@ __device__ __forceinline__ void decompose_coeff(u32 t, u32 Q, u32 qhalf, int gbi
         d  = (d - r0) >> gbits;
         out[k] = min((u32)r0, (u32)r0 + Q);   // r0 < 0 ? r0 + Q : r0 as one VIADDMNMX.U32 (a negative r0 is > r0 + Q unsigned)
     }
+}
+
+// 64-bit sum -> [0, 4Q): the N = 2048 kernels take the wide-constant form (their Q may have 29 or 30 bits)
+template <int LOGN>
+__device__ __forceinline__ u32 red64(u64 x, const BrParams& P, u32 Q) {
+    if (LOGN >= 11) return reduce64x(x, P.red_s, P.red_mu, P.red_mu_hi, Q);
+    return reduce64(x, P.red_s, P.red_mu, Q);
 }
 
 __device__ __forceinline__ void pair_barrier(int id) {

@@ -112,11 +112,11 @@ __device__ __forceinline__ void mac_ginx(u32 (&acc)[(1 << LOGN) / 32], const u32
                 s2 = mad_wide(d, comp4(o2[k], e), s2);
                 s2 = mad_wide(x, comp4(p2[k], e), s2);
             }
-            const u32 r1 = reduce64(s1, P.red_s, P.red_mu, Q);
-            const u32 r2 = reduce64(s2, P.red_s, P.red_mu, Q);
+            const u32 r1 = red64<LOGN>(s1, P, Q);
+            const u32 r2 = red64<LOGN>(s2, P, Q);
             u64 t        = mad_wide(r1, comp4(m1, e), (u64)acc[4 * v + e]);
             t            = mad_wide(r2, comp4(m2, e), t);
-            acc[4 * v + e] = csub(reduce64(t, P.red_s, P.red_mu, Q), Q2);
+            acc[4 * v + e] = csub(red64<LOGN>(t, P, Q), Q2);
         }
     }
 }
@@ -147,7 +147,7 @@ __device__ __forceinline__ void mac_replace(u32 (&acc)[(1 << LOGN) / 32], const 
                 s1 = mad_wide(dg[k][4 * v + e], comp4(o1[k], e), s1);
                 s1 = mad_wide(comp4(dx[k], e), comp4(p1[k], e), s1);
             }
-            acc[4 * v + e] = csub(reduce64(s1, P.red_s, P.red_mu, Q), Q2);
+            acc[4 * v + e] = csub(red64<LOGN>(s1, P, Q), Q2);
         }
     }
 }
@@ -223,7 +223,7 @@ template <int LOGN, int LOGH, int ROWS, int CTS>
 __global__ void __launch_bounds__(64 * CTS, 1)
 br_ginx_kernel(const __grid_constant__ BrParams P) {
     using W         = WNtt<LOGN, LOGH>;
-    constexpr bool STAGE = (ROWS == 4);   // see GinxSmem
+    constexpr bool STAGE = (ROWS == 4 && LOGN <= 10);   // see GinxSmem; the N = 2048 key pair (128 KB) does not fit
     using S         = typename std::conditional<STAGE, GinxSmem<LOGN, LOGH, ROWS, CTS>, BrSmem<LOGN, LOGH, ROWS, CTS>>::type;
     constexpr int N = W::N, E = W::E;
     extern __shared__ __align__(16) unsigned char smem_raw[];

@@ -10,7 +10,7 @@ enum : u32 { OP_END = 0u, OP_EXT = 1u << 30, OP_AUTO = 2u << 30, OP_PERM1 = 3u <
 // ---- schedules -------------------------------------------------------------------------------------------------
 // AP: for i < n, k < digitsR: a0 = k-th base-baseR digit of (0 - a_i mod q) [u64 arithmetic exactly as
 // NativeInteger::ModSubFast + Mod + /=]; if a0 != 0 -> ext-product with ek[i][a0][k]
-__global__ void sched_ap_kernel(const u32* __restrict__ a, u32* __restrict__ sched, u32 n, u32 stride, u64 q, u32 baseR,
+static __global__ void sched_ap_kernel(const u32* __restrict__ a, u32* __restrict__ sched, u32 n, u32 stride, u64 q, u32 baseR,
                                 u32 digitsR, u64 count) {
     const u64 ct = (u64)blockIdx.x * blockDim.x + threadIdx.x;
     if (ct >= count) return;
@@ -30,7 +30,7 @@ __global__ void sched_ap_kernel(const u32* __restrict__ a, u32* __restrict__ sch
 
 // LMKCDEY: one warp per ciphertext; buckets by logGen[(-a_i mod 2N) | 1] (ascending i inside a bucket), then the
 // two sweeps i = N/2-1 .. 1 with automorphisms every numAutoKeys skips (rgsw-acc-lmkcdey.cpp:83-157).
-__global__ void __launch_bounds__(32) sched_lmkcdey_kernel(const u32* __restrict__ a, const i32* __restrict__ logGen,
+static __global__ void __launch_bounds__(32) sched_lmkcdey_kernel(const u32* __restrict__ a, const i32* __restrict__ logGen,
                                                            u32* __restrict__ sched, u32 n, u32 stride, u32 N, u32 w) {
     extern __shared__ i32 sm_s[];
     const u32 Nh = N / 2, M = 2 * N;
@@ -115,7 +115,7 @@ __device__ __forceinline__ void mac_auto_split(u32 (&acc)[(1 << LOGN) / 32], con
 #pragma unroll
             for (int d = 0; d < ND; ++d)
                 s = mad_wide((d >= LO && d < HI) ? dg[d][4 * v + e] : comp4(dx[d], e), comp4(k1[d], e), s);
-            acc[4 * v + e] = csub(reduce64(s, P.red_s, P.red_mu, Q), Q2);
+            acc[4 * v + e] = csub(red64<LOGN>(s, P, Q), Q2);
         }
     }
 }

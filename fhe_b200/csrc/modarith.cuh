@@ -33,6 +33,13 @@ __device__ __forceinline__ u32 reduce64(u64 x, u32 s, u32 mu, u32 Q) {
     u32 q  = __umulhi(xh, mu);
     return (u32)x - q * Q;
 }
+// The same with mu = floor(2^(s+32) / Q) of up to 34 bits (Q of 29 or 30 bits, where 2^s exceeds Q): only the low 32 bits of the
+// quotient estimate enter x - q Q mod 2^32, so the high part of mu is one more multiply-add.
+__device__ __forceinline__ u32 reduce64x(u64 x, u32 s, u32 mu, u32 mu_hi, u32 Q) {
+    u32 xh = (u32)(x >> s);
+    u32 q  = __umulhi(xh, mu) + xh * mu_hi;
+    return (u32)x - q * Q;
+}
 __device__ __forceinline__ u64 mad_wide(u32 a, u32 b, u64 c) {
     return (u64)a * b + c;
 }

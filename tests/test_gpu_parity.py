@@ -542,6 +542,52 @@ def test_wide_custom_params_all_methods(method, bits, N, baseG, qKS):
     ctx.close(); oc.close()
 
 
+# ---- key-ordered key switch (ks_tile.cuh): the 16-bit keys of the qKS = 2^14, baseKS = 32 sets ---------------------------------
+@pytest.mark.parametrize("n,N,method,cnt", [(503, 1024, "GINX", 700), (447, 1024, "LMKCDEY", 257), (40, 512, "GINX", 1000)])
+def test_keyswitch_tile_vs_oracle_and_gather_kernel(n, N, method, cnt, monkeypatch):
+    """ks_tile_kernel (forced with LUXB200_KS_TILE=1; large batches pick it by themselves) against the oracle's KeySwitch
+    (lwe-pke.cpp:348-372) on every ciphertext, against keyswitch_kernel (LUXB200_KS_TILE=0) word for word, and inside
+    SwitchCTtoqn (both ModSwitches) through gates against the oracle.  Batch sizes with a partial tile and partial warps."""
+    from fhe_b200.context import BinFHEContext
+    O = oracle()
+    ctx = BinFHEContext()
+    Q = ctx.L.luxb200_last_prime(27, 2 * N)
+    ctx.GenerateFromParams(n=n, N=N, q=N, Q=Q, qKS=16384, baseKS=32, baseG=512 if method == "GINX" else 1024, baseR=32,
+                           numAutoKeys=10, method=method)
+    oc = oracle_twin(ctx, method)
+    sk, bsk, A, B = oc.keygen(seed=n + N)
+    ctx.BTKeyLoad(bsk, A, B)
+    rng = np.random.default_rng(n * N)
+    ka = rng.integers(0, 16384, size=(cnt, N), dtype=np.uint64); kb = rng.integers(0, 16384, size=cnt, dtype=np.uint64)
+    ka[0, :] = 16383; ka[1, :] = 0; ka[2, ::2] = 0
+    monkeypatch.setenv("LUXB200_KS_TILE", "1")
+    ta, tb = ctx.KeySwitchBatch((ka, kb))
+    monkeypatch.setenv("LUXB200_KS_TILE", "0")
+    ga, gb = ctx.KeySwitchBatch((ka, kb))
+    assert (ta == ga).all() and (tb == gb).all()
+    for i in range(cnt):
+        xa = np.zeros(ctx.n, np.uint64); xb = np.zeros(1, np.uint64)
+        O.orc_keyswitch(oc.h, P(np.ascontiguousarray(ka[i])), int(kb[i]), P(xa), P(xb))
+        assert (ta[i] == xa).all() and tb[i] == xb[0], i
+    # through SwitchCTtoqn: gates, tile vs gather on the whole batch and vs the oracle on a few
+    g = 300
+    a1 = np.zeros((g, ctx.n), np.uint64); b1 = np.zeros(g, np.uint64); a2 = a1.copy(); b2 = b1.copy()
+    for i in range(g):
+        a1[i], b1[i] = oc.encrypt(sk, i & 1, 3 * i + 1)
+        a2[i], b2[i] = oc.encrypt(sk, (i >> 1) & 1, 3 * i + 2)
+    monkeypatch.setenv("LUXB200_KS_TILE", "1")
+    (oa, ob), res = ctx.EvalBinGateBatch("NAND", (a1, b1), (a2, b2))
+    assert res.success, res.error
+    monkeypatch.setenv("LUXB200_KS_TILE", "0")
+    (pa, pb), res = ctx.EvalBinGateBatch("NAND", (a1, b1), (a2, b2))
+    assert res.success, res.error
+    assert (oa == pa).all() and (ob == pb).all()
+    idx = [0, 1, 15, 16, 255, 256, 299]
+    xa, xb = oc.evalbingate("NAND", a1[idx], b1[idx], a2[idx], b2[idx])
+    assert (oa[idx] == xa).all() and (ob[idx] == xb).all()
+    ctx.close(); oc.close()
+
+
 @pytest.mark.parametrize("logQ,time_opt", [(17, True), (27, True), (23, False), (13, False)])
 def test_largeprec_floor_sign_decomp(logQ, time_opt):
     """EvalFloor / EvalSign / EvalDecomp (binfhe-base-scheme.cpp:335-521) on the large-precision contexts of
