@@ -332,13 +332,22 @@ def method_metric(lib, local, dev, name, method, G, imad_peak):
         ctx.EvalBinGateBatch("AND", (a1[:1024], b1[:1024]), (a2[:1024], b2[:1024]))
     br = tot = wall = 0.0
     reps = 3
+    # pinned host buffers through the C ABI call, like the headline e2e (H2D + D2H inside the timed call)
+    import torch
+    from fhe_b200 import lib as _l
+    VP = _l.VP
+    h = [torch.from_numpy(np.ascontiguousarray(x).view(np.int64)).pin_memory() for x in (a1, b1, a2, b2)]
+    h_oa = torch.empty((G, ctx.n), dtype=torch.int64).pin_memory()
+    h_ob = torch.empty(G, dtype=torch.int64).pin_memory()
     for _ in range(reps):
         t0 = time.perf_counter()
-        (oa, ob), res = ctx.EvalBinGateBatch("AND", (a1, b1), (a2, b2))
+        rc = lib.luxb200_evalbingate_batch(ctx.h, _l.GATE["AND"], VP(h[0].data_ptr()), VP(h[1].data_ptr()), VP(h[2].data_ptr()),
+                                           VP(h[3].data_ptr()), VP(h_oa.data_ptr()), VP(h_ob.data_ptr()), G, 0)
         wall += time.perf_counter() - t0
-        assert res.success, res.error
+        assert rc == 0, lib.luxb200_last_error().decode()
         tm = ctx.LastTiming()
         br += tm["br_ms"]; tot += tm["total_ms"]
+    oa = h_oa.numpy().view(np.uint64); ob = h_ob.numpy().view(np.uint64)
     errors = int((kg.decrypt(ctx, ks.sk, oa, ob) != (m1 & m2)).sum())
     s = (a1 + a2) % ctx.q          # the blind rotation runs on ct1 + ct2 (AND)
     EXT, AUTO = 6 * 5120 * 3 + 8 * 1024 * 4, 3 * 5120 * 3 + 4 * 1024 * 4
@@ -369,6 +378,40 @@ def method_metric(lib, local, dev, name, method, G, imad_peak):
         out["roofline"]["note"] = ("even if every key byte the op lists touch came from DRAM the stream would need about a third of "
                                    "the HBM peak; the CTAs walk i together, so most of the 1 GB key is served from L2 (ncu "
                                    "r1_sched_ap_v0: L2 hit 93 %): the integer pipe binds, not HBM (SURVEY 8(d) expected HBM)")
+    ctx.close()
+    return out
+
+
+def n2048_metric(lib, local, name, G, imad_peak):
+    """The N = 2048 GINX parameter sets (judge-added row of SURVEY 8): G gates on random keys and inputs (throughput does not
+    depend on their values; parity of these sets is tests/test_gpu_parity.py::test_wide_sets_vs_oracle), device-timed.
+    Roofline for the 32-bit sets against the live IMAD probe: per step (2 INTT + rows NTT) x N/2 log2 N butterflies x 3 IMAD +
+    2 keys x rows x 2 x N pointwise x 4 IMAD; the 64-bit sets report throughput only."""
+    from fhe_b200.context import BinFHEContext
+    rng = np.random.default_rng(1)
+    ctx = BinFHEContext(device=local).GenerateBinFHEContext(name, "GINX")
+    bsk = rng.integers(0, ctx.Q, size=ctx.bsk_len(), dtype=np.uint64)
+    A = rng.integers(0, ctx.qKS, size=ctx.ksk_rows() * ctx.n, dtype=np.uint64)
+    B = rng.integers(0, ctx.qKS, size=ctx.ksk_rows(), dtype=np.uint64)
+    ctx.BTKeyLoad(bsk, A, B)
+    del bsk, A
+    a1 = rng.integers(0, ctx.q, size=(G, ctx.n), dtype=np.uint64); b1 = rng.integers(0, ctx.q, size=G, dtype=np.uint64)
+    a2 = rng.integers(0, ctx.q, size=(G, ctx.n), dtype=np.uint64); b2 = rng.integers(0, ctx.q, size=G, dtype=np.uint64)
+    ctx.EvalBinGateBatch("AND", (a1[:148], b1[:148]), (a2[:148], b2[:148]))
+    (oa, ob), res = ctx.EvalBinGateBatch("AND", (a1, b1), (a2, b2))
+    assert res.success, res.error
+    t = ctx.LastTiming()
+    N, n, rows = ctx.N, ctx.n, ctx.rows
+    out = {"workload": f"{name} GINX EvalBinGate(AND) x{G} (n={n}, N={N}, {int(ctx.Q).bit_length()}-bit Q, {rows // 2} digits, random keys)",
+           "value": G / (t["total_ms"] * 1e-3), "unit": "bootstraps/s", "br_ms": t["br_ms"]}
+    if ctx.Q < (1 << 30):
+        steps = float(((a1 + a2) % ctx.q != 0).sum()) / G     # X^0 - 1 = 0 steps are skipped by the shared-memory kernel
+        per_step = (2 + rows) * (N // 2) * (N.bit_length() - 1) * 3 + 2 * rows * 2 * N * 4
+        achieved = G * n * per_step / (t["br_ms"] * 1e-3)
+        out["roofline"] = {"bound": "int32-pipe", "kernel": "br_ginx_kernel<11,..> (br11.cu)" if rows == 4 else "brw_kernel<u32>",
+                           "achieved": achieved / 1e12, "peak": imad_peak / 1e12, "unit": "TIMAD/s",
+                           "frac": achieved / imad_peak if imad_peak else None, "algorithmic_imad_per_gate": n * per_step,
+                           "nonzero_steps_per_gate": steps}
     ctx.close()
     return out
 
@@ -594,6 +637,7 @@ def main():
         extras["ntt32_n2048"] = ntt32_metric(lib, local, dev, 2048, 29)
         extras["lmkcdey"] = method_metric(lib, local, dev, "STD128_LMKCDEY", "LMKCDEY", 16384, imad_v)
         extras["ap"] = method_metric(lib, local, dev, "STD128_AP", "AP", 4096, imad_v)
+        extras["n2048"] = {k: n2048_metric(lib, local, k, 1184, imad_v) for k in ("STD256", "STD256_3", "STD192")}
 
     cpu_baseline = None
     if not args.no_cpu_baseline:
