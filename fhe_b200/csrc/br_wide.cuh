@@ -199,6 +199,8 @@ __device__ __forceinline__ void w_digits2(const T* acc, T* dig, u32 PL, const Br
     w_ntt_fwd(dig, 2 * P.nd, PL, P.logN, P);
 }
 
+// (a 64-register cap for u32 — four 52 KB CTAs per SM instead of three — moved the two-digit sets by +3 % and the three-digit ones
+// by -2 %: not kept, r2 job 20)
 template <typename T, int NT>
 __global__ void __launch_bounds__(NT) brw_kernel(const __grid_constant__ BrwParams<T> P) {
     typedef typename WideTraits<T>::Wide Wide;
