@@ -408,7 +408,7 @@ def n2048_metric(lib, local, name, G, imad_peak):
         steps = float(((a1 + a2) % ctx.q != 0).sum()) / G     # X^0 - 1 = 0 steps are skipped by the shared-memory kernel
         per_step = (2 + rows) * (N // 2) * (N.bit_length() - 1) * 3 + 2 * rows * 2 * N * 4
         achieved = G * n * per_step / (t["br_ms"] * 1e-3)
-        out["roofline"] = {"bound": "int32-pipe", "kernel": "br_ginx_kernel<11,..> (br11.cu)" if rows == 4 else "brw_kernel<u32>",
+        out["roofline"] = {"bound": "int32-pipe", "kernel": "br_quad_kernel (br11.cu)" if rows in (4, 6) else "brw_kernel<u32>",
                            "achieved": achieved / 1e12, "peak": imad_peak / 1e12, "unit": "TIMAD/s",
                            "frac": achieved / imad_peak if imad_peak else None, "algorithmic_imad_per_gate": n * per_step,
                            "nonzero_steps_per_gate": steps}
@@ -637,7 +637,8 @@ def main():
         extras["ntt32_n2048"] = ntt32_metric(lib, local, dev, 2048, 29)
         extras["lmkcdey"] = method_metric(lib, local, dev, "STD128_LMKCDEY", "LMKCDEY", 16384, imad_v)
         extras["ap"] = method_metric(lib, local, dev, "STD128_AP", "AP", 4096, imad_v)
-        extras["n2048"] = {k: n2048_metric(lib, local, k, 1184, imad_v) for k in ("STD256", "STD256_3", "STD192")}
+        # 1776 gates = whole waves for 3 (two digits), 2 (three digits) and 3 (shared-memory kernel) ciphertexts per SM
+        extras["n2048"] = {k: n2048_metric(lib, local, k, 1776, imad_v) for k in ("STD256", "STD256_3", "STD192")}
 
     cpu_baseline = None
     if not args.no_cpu_baseline:

@@ -56,7 +56,10 @@ def build(force=False, verbose=False):
     procs = []
     for u in UNITS:
         if force or _stale(u):
-            cmd = [NVCC] + FLAGS + ["-c", "-o", _obj(u), os.path.join(CSRC, u)]
+            # br11.cu is 16 large kernels: its optimisation passes run on all host cores (api.cu keeps the single-threaded
+            # pipeline its tuned kernels were measured with)
+            extra = ["--split-compile", "0"] if u == "br11.cu" else []
+            cmd = [NVCC] + FLAGS + extra + ["-c", "-o", _obj(u), os.path.join(CSRC, u)]
             procs.append((cmd, subprocess.Popen(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)))
     failed = False
     for cmd, p in procs:

@@ -35,13 +35,30 @@ static inline unsigned nblk(uint64_t total, unsigned bs) { return (unsigned)((to
 // ---- u32 NTT tables -------------------------------------------------------------------------------------------
 int Ntt32Tables::build(uint32_t N_, uint64_t Q_, uint64_t psi_) {
     using namespace lb;
-    N = N_; Q = Q_; psi = psi_;
+    std::vector<uint64_t> tw, twi;
+    ntt_tables(N_, Q_, psi_, tw, twi);
+    psi = psi_;
+    return build_from(N_, Q_, tw, twi, invmod_prime(N_ % Q_, Q_));
+}
+// Half h of a 2N-point transform as an N-point one (br_quad.cuh): after the first Cooley-Tukey stage the two halves are
+// independent N-point transforms whose stage-m twiddles are the 2N-point table's entries 2m + h m + i; ninv2 = (2N)^-1
+int Ntt32Tables::build_half(uint32_t N_, uint64_t Q_, const std::vector<uint64_t>& tw2, const std::vector<uint64_t>& twi2,
+                            uint32_t h, uint64_t ninv2) {
+    std::vector<uint64_t> tw(N_, 1), twi(N_, 1);
+    for (uint32_t m = 1; m < N_; m <<= 1)
+        for (uint32_t i = 0; i < m; ++i) {
+            tw[m + i]  = tw2[2 * m + h * m + i];
+            twi[m + i] = twi2[2 * m + h * m + i];
+        }
+    return build_from(N_, Q_, tw, twi, ninv2);
+}
+int Ntt32Tables::build_from(uint32_t N_, uint64_t Q_, const std::vector<uint64_t>& tw, const std::vector<uint64_t>& twi, uint64_t ninv) {
+    using namespace lb;
+    N = N_; Q = Q_;
     logN = ilog2(N);
     if (Q >= (1ull << 30)) return lb_fail(LUXB200_ERR_UNSUPPORTED, "u32 NTT path needs Q < 2^30 (got %llu)", (unsigned long long)Q);
     logH = 32 - bits_of(Q);
     if (logH > 5) logH = 5;
-    std::vector<uint64_t> tw, twi;
-    ntt_tables(N, Q, psi, tw, twi);
     const uint32_t E = N / 32, TB = (E / 2 < 16) ? E / 2 : 16;
     memset(&C, 0, sizeof(C));
     for (uint32_t i = 1; i < E && i < 64; ++i) {
@@ -50,7 +67,6 @@ int Ntt32Tables::build(uint32_t N_, uint64_t Q_, uint64_t psi_) {
     }
     C.Q = (u32)Q; C.Q2 = (u32)(2 * Q); C.mu32 = (u32)((1ull << 32) / Q);
     for (int k = 0; k < 8; ++k) C.QM[k] = (u32)(Q << k);   // only multiples below 2^32 are ever used (bounds <= 2^LOGH)
-    uint64_t ninv = invmod_prime(N % Q, Q);
     C.ninv = (u32)ninv; C.ninv_s = shoup32(ninv, Q);
     uint64_t w1 = mulmod(twi[1], ninv, Q);
     C.w1ninv = (u32)w1; C.w1ninv_s = shoup32(w1, Q);
@@ -126,6 +142,7 @@ int lb_build_wide_tables(luxb200_ctx* c) {
                          cudaMemcpy(W.pw.p, pw32.data(), 2 * (size_t)N * 4, cudaMemcpyHostToDevice) != cudaSuccess))
                 rcw = lb_fail(LUXB200_ERR_CUDA, "table upload failed");
         }
+    if (!rcw && cudaDeviceSynchronize() != cudaSuccess) rcw = lb_fail(LUXB200_ERR_CUDA, "table upload failed");   // the pageable uploads have landed
     return rcw;
 }
 
@@ -169,12 +186,22 @@ int luxb200_ctx_create(const luxb200_params* p, int device, luxb200_ctx** out) {
     if ((u128_t)p->qKS * p->N * c->digitsKS >= ((u128_t)1 << 64)) { luxb200_ctx_destroy(c); return lb_fail(LUXB200_ERR_UNSUPPORTED, "qKS too large for the key-switch accumulator"); }
     // the register-resident warp-pair kernels cover N = 1024 with 2 or 3 digits and N = 512 with 2, Q < 2^30; everything else
     // (N = 2048, 64-bit Q, 1 / 4 / 5 digits) runs the shared-memory kernel of br_wide.cuh
-    // (r2: N = 2048 GINX with 2 digits also fits the register-resident kernel — 64 coefficients per lane, 255 registers, 4
-    // ciphertexts per SM: 1.34x the shared-memory kernel.  Its step body no longer fits the instruction caches (ncu: 2.3
-    // no_instruction stalls per issue), and the scheduled kernel at that size is slower than br_wide.cuh, so AP / LMKCDEY at
-    // N = 2048 stay there.)
-    const bool fast = p->Q < (1ull << 30) && ((c->logN == 10 && (c->rows == 4 || c->rows == 6)) || (c->logN == 9 && c->rows == 4) ||
-                                               (c->logN == 11 && c->rows == 4 && p->Q >= (1ull << 27) && p->method == LUXB200_GINX));
+    // r2: N = 2048 with 2 or 3 digits (GINX and AP) runs the same register-resident code as four warps per ciphertext
+    // (br_quad.cuh); LMKCDEY at N = 2048 (cross-half automorphism gathers) stays on br_wide.cuh
+    c->quad = p->Q < (1ull << 30) && p->Q >= (1ull << 24) && c->logN == 11 && (c->rows == 4 || c->rows == 6) && p->method != LUXB200_LMKCDEY;
+    if (c->quad && bits_of(p->Q) < 30) {
+        // below 30 bits these kernels use reduce64x, which leaves less than (xmax / 2^(s+32) + 2^s / Q + 1) Q: that must stay
+        // under 4Q (it is 3.0 / 3.75 for the 29-bit sets with two / three digits); a modulus that leaves no margin runs wide
+        const u128_t Q = p->Q;
+        u128_t xmax = (u128_t)c->rows * 2 * Q * Q;
+        if (8 * Q * Q + 4 * Q > xmax) xmax = 8 * Q * Q + 4 * Q;
+        uint32_t b = 0;
+        while ((xmax >> b) != 0) ++b;
+        const int s = b > 32 ? (int)b - 32 : 0;
+        const long double bound = (long double)xmax / std::ldexp(1.0L, s + 32) + std::ldexp(1.0L, s) / (long double)p->Q + 1.0L;
+        if (bound > 3.999L) c->quad = false;
+    }
+    const bool fast = p->Q < (1ull << 30) && ((c->logN == 10 && (c->rows == 4 || c->rows == 6)) || (c->logN == 9 && c->rows == 4) || c->quad);
     c->wide.on = !fast;
     if (c->wide.on) {
         luxb200_ctx::Wide& W = c->wide;
@@ -195,14 +222,32 @@ int luxb200_ctx_create(const luxb200_params* p, int device, luxb200_ctx** out) {
         uint32_t b = 0;
         while ((xmax >> b) != 0) ++b;
         uint32_t s = b > 32 ? b - 32 : 0;
-        // mu = floor(2^(s+32) / Q): below 2^32 when 2^s < Q; the N = 2048 kernels (reduce64x) take up to 34 bits
+        // mu = floor(2^(s+32) / Q) fits 32 bits and the truncated Barrett step keeps its error bound when 2^s < Q; the N = 2048
+        // kernels reduce in two words instead (reduce64w: any x < 2^64) and carry R = 2^32 mod Q with its Shoup companion
         const u128_t mu = (((u128_t)1) << (s + 32)) / Q;
-        if ((mu >> 32) != 0 && (c->logN < 11 || (mu >> 34) != 0)) { luxb200_ctx_destroy(c); return lb_fail(LUXB200_ERR_UNSUPPORTED, "Q too large for the 64->32 reduction (rows=%u)", c->rows); }
-        c->red_s = s;
-        c->red_mu = (uint32_t)mu;
-        c->red_mu_hi = (uint32_t)(mu >> 32);
+        if (c->quad) {
+            if (b > 64) { luxb200_ctx_destroy(c); return lb_fail(LUXB200_ERR_UNSUPPORTED, "Q too large for the 64-bit accumulation (rows=%u)", c->rows); }
+            const uint64_t R = (uint64_t)((((u128_t)1) << 32) % Q);
+            c->red_r = (uint32_t)R; c->red_rs = shoup32(R, p->Q);
+            c->red_s = s; c->red_mu = (uint32_t)mu; c->red_mu_hi = (uint32_t)(mu >> 32);
+        } else {
+            if ((mu >> 32) != 0) { luxb200_ctx_destroy(c); return lb_fail(LUXB200_ERR_UNSUPPORTED, "Q too large for the 64->32 reduction (rows=%u)", c->rows); }
+            c->red_s = s;
+            c->red_mu = (uint32_t)mu;
+            c->red_mu_hi = 0;
+        }
     }
-    rc = c->ntt.build(p->N, p->Q, c->p.psi);
+    if (c->quad) {
+        std::vector<uint64_t> tw2, twi2;
+        ntt_tables(p->N, p->Q, c->p.psi, tw2, twi2);
+        const uint64_t ninv2 = invmod_prime(p->N % p->Q, p->Q);
+        rc = c->ntt.build_half(p->N / 2, p->Q, tw2, twi2, 0, ninv2);
+        if (!rc) rc = c->ntt1.build_half(p->N / 2, p->Q, tw2, twi2, 1, ninv2);
+        c->xw = (uint32_t)tw2[1]; c->xws = shoup32(tw2[1], p->Q);
+        c->xwi = (uint32_t)twi2[1]; c->xwis = shoup32(twi2[1], p->Q);
+    } else {
+        rc = c->ntt.build(p->N, p->Q, c->p.psi);
+    }
     }
     if (rc) { luxb200_ctx_destroy(c); return rc; }
     cudaError_t e = cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking);
@@ -211,7 +256,8 @@ int luxb200_ctx_create(const luxb200_params* p, int device, luxb200_ctx** out) {
     if (p->method == LUXB200_GINX && !c->wide.on) {
         // monomials X^a - 1 in EVALUATION format (rgsw-cryptoparameters.cpp:96-113), sigma order:
         // value at index p is psi^(a (2 brv(p) + 1)) - 1
-        const uint32_t N = p->N, M = 2 * N, E = N / 32;
+        const uint32_t N = p->N, M = 2 * N;
+        const uint32_t E = (c->quad ? N / 2 : N) / 32, HM = c->quad ? N / 2 - 1 : N - 1;   // quad: [h][sigma order of p mod 1024]
         std::vector<uint64_t> pw(M);
         pw[0] = 1;
         for (uint32_t i = 1; i < M; ++i) pw[i] = mulmod(pw[i - 1], c->p.psi, p->Q);
@@ -220,9 +266,9 @@ int luxb200_ctx_create(const luxb200_params* p, int device, luxb200_ctx** out) {
         for (uint32_t pp = 0; pp < N; ++pp) odd[pp] = 2 * bitrev(pp, c->logN) + 1;
         for (uint32_t a = 0; a < M; ++a)
             for (uint32_t pp = 0; pp < N; ++pp) {
-                const uint32_t l = pp / E, r = pp % E;
+                const uint32_t ps = pp & HM, l = ps / E, r = ps % E;
                 const uint64_t v = pw[((uint64_t)a * odd[pp]) % M];
-                h[(size_t)a * N + (r >> 2) * 128 + 4 * l + (r & 3)] = (u32)(v ? v - 1 : p->Q - 1);
+                h[(size_t)a * N + (pp - ps) + (r >> 2) * 128 + 4 * l + (r & 3)] = (u32)(v ? v - 1 : p->Q - 1);
             }
         rc = c->mono.ensure(h.size() * 4);
         if (!rc && cudaMemcpy(c->mono.p, h.data(), h.size() * 4, cudaMemcpyHostToDevice) != cudaSuccess)
@@ -275,6 +321,9 @@ int luxb200_ctx_create(const luxb200_params* p, int device, luxb200_ctx** out) {
     // KSK element type
     c->ks_elem = (p->qKS <= 65536) ? 2 : (p->qKS <= (1ull << 32)) ? 4 : 8;
     c->npad = (p->n + 7) & ~7u;
+    // the table uploads above were synchronous copies from pageable memory, which may return before their DMA has landed; the
+    // context's non-blocking stream does not order itself behind them
+    if (cudaDeviceSynchronize() != cudaSuccess) { luxb200_ctx_destroy(c); return lb_fail(LUXB200_ERR_CUDA, "table upload failed"); }
     *out = c;
     return 0;
 }
@@ -288,7 +337,7 @@ void luxb200_ctx_destroy(luxb200_ctx* c) {
                       &c->xin};
     for (DevBuf* b : bufs) b->release();
     c->wide.tw.release(); c->wide.twi.release(); c->wide.pw.release(); c->wide.automap.release();
-    c->ntt.release();
+    c->ntt.release(); c->ntt1.release();
     for (int s = 0; s < 2; ++s) {
         for (DevBuf& b : c->pipe.in[s]) b.release();
         for (DevBuf& b : c->pipe.st[s]) b.release();
@@ -350,7 +399,7 @@ int luxb200_load_bsk(luxb200_ctx* c, const uint64_t* bsk, int on_device) {
             src = stage.as<u64>();
         }
         if (c->wide.on) narrow_u64_u32_kernel<<<nblk(m, 256), 256, 0, c->stream>>>(src, c->bsk.as<u32>() + off, m);
-        else pack_polys_sigma_kernel<<<nblk(m, 256), 256, 0, c->stream>>>(src, c->bsk.as<u32>() + off, c->logN, m);
+        else pack_polys_sigma_kernel<<<nblk(m, 256), 256, 0, c->stream>>>(src, c->bsk.as<u32>() + off, c->logN, m, c->quad ? 1 : 0);
         c->launches++;
     }
     LB_CUDA(cudaStreamSynchronize(c->stream));

@@ -70,6 +70,8 @@ struct Ntt32Tables {
     NttConsts C;
     DevBuf twB, twiB, twfull, twifull;
     int build(uint32_t N, uint64_t Q, uint64_t psi);
+    int build_half(uint32_t N, uint64_t Q, const std::vector<uint64_t>& tw2, const std::vector<uint64_t>& twi2, uint32_t h, uint64_t ninv2);
+    int build_from(uint32_t N, uint64_t Q, const std::vector<uint64_t>& tw, const std::vector<uint64_t>& twi, uint64_t ninv);
     void release() { twB.release(); twiB.release(); twfull.release(); twifull.release(); }
 };
 
@@ -83,7 +85,11 @@ struct luxb200_ctx {
     uint32_t digitsG = 0, digitsKS = 0, digitsR = 0, rows = 0, logN = 0;
     uint32_t npad = 0;       // padded KSK row length
     uint32_t ks_elem = 0;    // bytes per KSK element (2 or 4)
-    uint32_t red_s = 0, red_mu = 0, red_mu_hi = 0;
+    uint32_t red_s = 0, red_mu = 0, red_mu_hi = 0, red_r = 0, red_rs = 0;
+    // br_quad.cuh (N = 2048 as four warps per ciphertext): `ntt` holds the twiddle set of half 0, `ntt1` of half 1
+    bool quad = false;
+    Ntt32Tables ntt1;
+    uint32_t xw = 0, xws = 0, xwi = 0, xwis = 0;   // cross-stage twiddles table[1], inverse table[1] (with Shoup companions)
     cudaStream_t stream = nullptr;
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     Ntt32Tables ntt;
@@ -119,7 +125,7 @@ struct luxb200_ctx {
 };
 
 int lb_set_device(int device);
-int lb_launch_br11(luxb200_ctx* c, const BrParams& P, int sched_only);   // br11.cu
+int lb_launch_quad(luxb200_ctx* c, const BrParams& P, int sched_only);   // br11.cu
 int lb_build_wide_tables(luxb200_ctx* c);
 #define LB_LOCK(c) std::lock_guard<std::recursive_mutex> lb_guard_((c)->mu)
 

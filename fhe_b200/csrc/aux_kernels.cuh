@@ -4,23 +4,24 @@
 
 // ---- key packing -------------------------------------------------------------------------------------------
 // canonical u64 polynomials (EVALUATION order p) -> u32, sigma order: p = E*l + r  ->  (r/4)*128 + 4*l + (r%4)
-__global__ void pack_polys_sigma_kernel(const u64* __restrict__ in, u32* __restrict__ out, u32 logN, u64 total) {
+// quad = 1 (br_quad.cuh): a polynomial is two halves of N/2 evaluation points, each in the sigma order of its own indices
+__global__ void pack_polys_sigma_kernel(const u64* __restrict__ in, u32* __restrict__ out, u32 logN, u64 total, u32 quad = 0) {
     const u64 idx = (u64)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= total) return;
-    const u32 N = 1u << logN, E = N >> 5;
+    const u32 N = 1u << logN, S = N >> quad, E = S >> 5;
     const u64 poly = idx >> logN;
-    const u32 p = (u32)(idx & (N - 1));
-    const u32 l = p / E, r = p % E;
-    out[poly * N + (r >> 2) * 128 + 4 * l + (r & 3)] = (u32)in[idx];
+    const u32 p = (u32)(idx & (N - 1)), ps = p & (S - 1);
+    const u32 l = ps / E, r = ps % E;
+    out[poly * N + (p - ps) + (r >> 2) * 128 + 4 * l + (r & 3)] = (u32)in[idx];
 }
-__global__ void unpack_polys_sigma_kernel(const u32* __restrict__ in, u64* __restrict__ out, u32 logN, u64 total) {
+__global__ void unpack_polys_sigma_kernel(const u32* __restrict__ in, u64* __restrict__ out, u32 logN, u64 total, u32 quad = 0) {
     const u64 idx = (u64)blockIdx.x * blockDim.x + threadIdx.x;
     if (idx >= total) return;
-    const u32 N = 1u << logN, E = N >> 5;
+    const u32 N = 1u << logN, S = N >> quad, E = S >> 5;
     const u64 poly = idx >> logN;
-    const u32 p = (u32)(idx & (N - 1));
-    const u32 l = p / E, r = p % E;
-    out[idx] = in[poly * N + (r >> 2) * 128 + 4 * l + (r & 3)];
+    const u32 p = (u32)(idx & (N - 1)), ps = p & (S - 1);
+    const u32 l = ps / E, r = ps % E;
+    out[idx] = in[poly * N + (p - ps) + (r >> 2) * 128 + 4 * l + (r & 3)];
 }
 // KSK A: u64 [rows][n] -> KT [rows][npad] (zero padded)
 template <typename KT>

@@ -33,7 +33,8 @@ struct BrParams {
     u32 mode;              // 0: lut prologue + extract epilogue, 1: acc_io in/out (raw EvalAcc)
     u32 amul;              // GINX: 2N / ctmod
     u32 auto_off;          // LMKCDEY: u32 offset of the automorphism keys inside bsk
-    u32 red_mu_hi;         // bits 32.. of the reduce64 constant (N = 2048 sets with 29- / 30-bit Q; 0 otherwise)
+    u32 red_mu_hi;         // bits 32.. of the reduce64 constant (reduce64x, N = 2048)
+    u32 red_r, red_rs;     // 2^32 mod Q and its Shoup companion (reduce64w, N = 2048 with a 30-bit Q)
 };
 
 // sigma: storage position of EVALUATION index p = E*l + r, chosen so that a lane's 4 consecutive
@@ -58,10 +59,12 @@ __device__ __forceinline__ void decompose_coeff(u32 t, u32 Q, u32 qhalf, int gbi
     }
 }
 
-// 64-bit sum -> [0, 4Q): the N = 2048 kernels take the wide-constant form (their Q may have 29 or 30 bits)
-template <int LOGN>
+// 64-bit sum -> [0, 4Q).  RED 0: reduce64 (2^s < Q: every N <= 1024 set); 1: reduce64x (N = 2048, Q up to 29 bits, bound checked
+// on the host); 2: reduce64w (30-bit Q)
+template <int RED>
 __device__ __forceinline__ u32 red64(u64 x, const BrParams& P, u32 Q) {
-    if (LOGN >= 11) return reduce64x(x, P.red_s, P.red_mu, P.red_mu_hi, Q);
+    if (RED == 2) return reduce64w(x, P.red_r, P.red_rs, P.C.mu32, Q);
+    if (RED == 1) return reduce64x(x, P.red_s, P.red_mu, P.red_mu_hi, Q);
     return reduce64(x, P.red_s, P.red_mu, Q);
 }
 

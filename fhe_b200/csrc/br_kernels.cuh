@@ -71,7 +71,9 @@ __device__ __forceinline__ u32 comp4(const uint4& v, int e) {
 
 // ---- GINX accumulator update (rgsw-acc-cggi.cpp:132-150) -----------------------------------------------
 // acc[c] += (sum_row dct[row] * ek1[row][c]) * mono + (sum_row dct[row] * ek2[row][c]) * monoNeg
-template <int LOGN, int ROWS, bool SMEM_KEYS = false>
+// RS: elements between consecutive polynomials of a key block / exchange rows (the quad kernel of br_quad.cuh works on one
+// 1024-point half of 2048-element rows); XRED: the wide reduction constant (29- / 30-bit Q at N = 2048)
+template <int LOGN, int ROWS, bool SMEM_KEYS = false, int RS = (1 << LOGN), int RED = 0>
 __device__ __forceinline__ void mac_ginx(u32 (&acc)[(1 << LOGN) / 32], const u32 (&dg)[ROWS / 2][(1 << LOGN) / 32],
                                          const uint4* exch, const BrParams& P, const u32* ek1, const u32* ek2,
                                          const u32* mp, const u32* mn, int c, int lane) {
@@ -79,28 +81,28 @@ __device__ __forceinline__ void mac_ginx(u32 (&acc)[(1 << LOGN) / 32], const u32
     const u32 Q = P.C.Q, Q2 = P.C.Q2;
     // this warp's digit polynomials are rows 2k+c, the partner's rows 2k+1-c: the (runtime) warp parity goes into the key
     // row ADDRESS, not into a per-operand select of the digit
-    const uint4* k1o = reinterpret_cast<const uint4*>(ek1) + (size_t)(c * 2 + c) * (N / 4);         // row c,   component c
-    const uint4* k1p = reinterpret_cast<const uint4*>(ek1) + (size_t)((1 - c) * 2 + c) * (N / 4);   // row 1-c, component c
-    const uint4* k2o = reinterpret_cast<const uint4*>(ek2) + (size_t)(c * 2 + c) * (N / 4);
-    const uint4* k2p = reinterpret_cast<const uint4*>(ek2) + (size_t)((1 - c) * 2 + c) * (N / 4);
-    const uint4* xp  = exch + (1 - c) * (N / 4);
+    const uint4* k1o = reinterpret_cast<const uint4*>(ek1) + (size_t)(c * 2 + c) * (RS / 4);         // row c,   component c
+    const uint4* k1p = reinterpret_cast<const uint4*>(ek1) + (size_t)((1 - c) * 2 + c) * (RS / 4);   // row 1-c, component c
+    const uint4* k2o = reinterpret_cast<const uint4*>(ek2) + (size_t)(c * 2 + c) * (RS / 4);
+    const uint4* k2p = reinterpret_cast<const uint4*>(ek2) + (size_t)((1 - c) * 2 + c) * (RS / 4);
+    const uint4* xp  = exch + (1 - c) * (RS / 4);
 #pragma unroll
     for (int v = 0; v < E / 4; ++v) {
         uint4 o1[ND], p1[ND], o2[ND], p2[ND], dx[ND];
 #pragma unroll
         for (int k = 0; k < ND; ++k) {   // rows advance by 2 = 4 polynomials of N/4 vectors
             if (SMEM_KEYS) {             // ek1 / ek2 point into shared memory (GinxSmem::keys)
-                o1[k] = k1o[k * N + v * 32 + lane]; p1[k] = k1p[k * N + v * 32 + lane];
-                o2[k] = k2o[k * N + v * 32 + lane]; p2[k] = k2p[k * N + v * 32 + lane];
+                o1[k] = k1o[k * RS + v * 32 + lane]; p1[k] = k1p[k * RS + v * 32 + lane];
+                o2[k] = k2o[k * RS + v * 32 + lane]; p2[k] = k2p[k * RS + v * 32 + lane];
             } else {
-                o1[k] = __ldg(k1o + k * N + v * 32 + lane); p1[k] = __ldg(k1p + k * N + v * 32 + lane);
-                o2[k] = __ldg(k2o + k * N + v * 32 + lane); p2[k] = __ldg(k2p + k * N + v * 32 + lane);
+                o1[k] = __ldg(k1o + k * RS + v * 32 + lane); p1[k] = __ldg(k1p + k * RS + v * 32 + lane);
+                o2[k] = __ldg(k2o + k * RS + v * 32 + lane); p2[k] = __ldg(k2p + k * RS + v * 32 + lane);
             }
         }
         const uint4 m1 = __ldg(reinterpret_cast<const uint4*>(mp) + v * 32 + lane);
         const uint4 m2 = __ldg(reinterpret_cast<const uint4*>(mn) + v * 32 + lane);
 #pragma unroll
-        for (int k = 0; k < ND; ++k) dx[k] = xp[2 * k * (N / 4) + v * 32 + lane];
+        for (int k = 0; k < ND; ++k) dx[k] = xp[2 * k * (RS / 4) + v * 32 + lane];
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
             u64 s1 = 0, s2 = 0;
@@ -112,32 +114,32 @@ __device__ __forceinline__ void mac_ginx(u32 (&acc)[(1 << LOGN) / 32], const u32
                 s2 = mad_wide(d, comp4(o2[k], e), s2);
                 s2 = mad_wide(x, comp4(p2[k], e), s2);
             }
-            const u32 r1 = red64<LOGN>(s1, P, Q);
-            const u32 r2 = red64<LOGN>(s2, P, Q);
+            const u32 r1 = red64<RED>(s1, P, Q);
+            const u32 r2 = red64<RED>(s2, P, Q);
             u64 t        = mad_wide(r1, comp4(m1, e), (u64)acc[4 * v + e]);
             t            = mad_wide(r2, comp4(m2, e), t);
-            acc[4 * v + e] = csub(red64<LOGN>(t, P, Q), Q2);
+            acc[4 * v + e] = csub(red64<RED>(t, P, Q), Q2);
         }
     }
 }
 
 // ---- AP / LMKCDEY accumulator update: acc[c] = sum_row dct[row] * ek[row][c]  (replace) ---------------
-template <int LOGN, int ROWS>
+template <int LOGN, int ROWS, int RS = (1 << LOGN), int RED = 0>
 __device__ __forceinline__ void mac_replace(u32 (&acc)[(1 << LOGN) / 32], const u32 (&dg)[ROWS / 2][(1 << LOGN) / 32],
                                             const uint4* exch, const BrParams& P, const u32* ek, int c, int lane) {
     constexpr int N = 1 << LOGN, E = N / 32, ND = ROWS / 2;
     const u32 Q = P.C.Q, Q2 = P.C.Q2;
-    const uint4* ko = reinterpret_cast<const uint4*>(ek) + (size_t)(c * 2 + c) * (N / 4);         // own rows 2k+c
-    const uint4* kp = reinterpret_cast<const uint4*>(ek) + (size_t)((1 - c) * 2 + c) * (N / 4);   // partner rows 2k+1-c
-    const uint4* xp = exch + (1 - c) * (N / 4);
+    const uint4* ko = reinterpret_cast<const uint4*>(ek) + (size_t)(c * 2 + c) * (RS / 4);         // own rows 2k+c
+    const uint4* kp = reinterpret_cast<const uint4*>(ek) + (size_t)((1 - c) * 2 + c) * (RS / 4);   // partner rows 2k+1-c
+    const uint4* xp = exch + (1 - c) * (RS / 4);
 #pragma unroll
     for (int v = 0; v < E / 4; ++v) {
         uint4 o1[ND], p1[ND], dx[ND];
 #pragma unroll
         for (int k = 0; k < ND; ++k) {
-            o1[k] = __ldg(ko + k * N + v * 32 + lane);
-            p1[k] = __ldg(kp + k * N + v * 32 + lane);
-            dx[k] = xp[2 * k * (N / 4) + v * 32 + lane];
+            o1[k] = __ldg(ko + k * RS + v * 32 + lane);
+            p1[k] = __ldg(kp + k * RS + v * 32 + lane);
+            dx[k] = xp[2 * k * (RS / 4) + v * 32 + lane];
         }
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
@@ -147,7 +149,7 @@ __device__ __forceinline__ void mac_replace(u32 (&acc)[(1 << LOGN) / 32], const 
                 s1 = mad_wide(dg[k][4 * v + e], comp4(o1[k], e), s1);
                 s1 = mad_wide(comp4(dx[k], e), comp4(p1[k], e), s1);
             }
-            acc[4 * v + e] = csub(red64<LOGN>(s1, P, Q), Q2);
+            acc[4 * v + e] = csub(red64<RED>(s1, P, Q), Q2);
         }
     }
 }
@@ -223,7 +225,7 @@ template <int LOGN, int LOGH, int ROWS, int CTS>
 __global__ void __launch_bounds__(64 * CTS, 1)
 br_ginx_kernel(const __grid_constant__ BrParams P) {
     using W         = WNtt<LOGN, LOGH>;
-    constexpr bool STAGE = (ROWS == 4 && LOGN <= 10);   // see GinxSmem; the N = 2048 key pair (128 KB) does not fit
+    constexpr bool STAGE = (ROWS == 4);   // see GinxSmem
     using S         = typename std::conditional<STAGE, GinxSmem<LOGN, LOGH, ROWS, CTS>, BrSmem<LOGN, LOGH, ROWS, CTS>>::type;
     constexpr int N = W::N, E = W::E;
     extern __shared__ __align__(16) unsigned char smem_raw[];

@@ -1,5 +1,5 @@
-// br_launch.cuh — launch configuration of the register-resident blind-rotation kernels (br_kernels.cuh, br_sched.cuh), shared by
-// api.cu (N = 512 / 1024) and br11.cu (N = 2048: a translation unit of its own so that the two compile side by side).
+// br_launch.cuh — launch configuration of the warp-pair blind-rotation kernels (br_kernels.cuh, br_sched.cuh; N = 512 / 1024).
+// N = 2048 is br_quad.cuh, launched from br11.cu.
 #pragma once
 #include "api_common.h"
 #include "br_sched.cuh"
@@ -9,8 +9,7 @@ static int launch_sched_t(luxb200_ctx* c, const BrParams& P) {
 #ifdef LB_SCHED_CTS   // A/B builds: ciphertexts per CTA of the scheduled kernel (2 warps each)
     constexpr int CTS = ROWS > 4 ? 4 : LB_SCHED_CTS;
 #else
-    // digitsG-1 = 3: more registers per thread, fewer ciphertexts per SM; N = 2048: 255 registers, 8 warps fill the register file
-    constexpr int CTS = (ROWS > 4 || LOGN > 10) ? 4 : 6;
+    constexpr int CTS = ROWS > 4 ? 4 : 6;   // digitsG-1 = 3: more registers per thread, fewer ciphertexts per SM
 #endif
     using S = BrSmem<LOGN, LOGH, ROWS, CTS>;
     const unsigned grid = (unsigned)((P.count + CTS - 1) / CTS);
@@ -24,8 +23,8 @@ static int launch_sched_t(luxb200_ctx* c, const BrParams& P) {
 template <int LOGN, int LOGH, int ROWS>
 static int launch_br_t(luxb200_ctx* c, const BrParams& P) {
     if (c->p.method == LUXB200_GINX) {
-        constexpr int CTS = (ROWS > 4 || LOGN > 10) ? 4 : 6;  // 12 warps (8 when digitsG-1 = 3 or N = 2048), one CTA per SM
-        using S = typename std::conditional<ROWS == 4 && LOGN <= 10, GinxSmem<LOGN, LOGH, ROWS, CTS>, BrSmem<LOGN, LOGH, ROWS, CTS>>::type;
+        constexpr int CTS = ROWS > 4 ? 4 : 6;  // 12 warps (8 when digitsG-1 = 3), one CTA per SM
+        using S = typename std::conditional<ROWS == 4, GinxSmem<LOGN, LOGH, ROWS, CTS>, BrSmem<LOGN, LOGH, ROWS, CTS>>::type;
         static_assert(sizeof(S) <= 232448, "GINX shared memory exceeds the 227 KB opt-in limit");
         const unsigned grid = (unsigned)((P.count + CTS - 1) / CTS);
         auto k = br_ginx_kernel<LOGN, LOGH, ROWS, CTS>;

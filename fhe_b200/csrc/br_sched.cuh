@@ -115,7 +115,7 @@ __device__ __forceinline__ void mac_auto_split(u32 (&acc)[(1 << LOGN) / 32], con
 #pragma unroll
             for (int d = 0; d < ND; ++d)
                 s = mad_wide((d >= LO && d < HI) ? dg[d][4 * v + e] : comp4(dx[d], e), comp4(k1[d], e), s);
-            acc[4 * v + e] = csub(red64<LOGN>(s, P, Q), Q2);
+            acc[4 * v + e] = csub(red64<0>(s, P, Q), Q2);
         }
     }
 }

@@ -137,8 +137,9 @@ __global__ void __launch_bounds__(128) kg_ksk_kernel(const __grid_constant__ KgP
 // storage position of EVALUATION index p of one polynomial: sigma order for the register-resident kernels, natural otherwise
 __device__ __forceinline__ u32 kg_pos(const KgParams& P, u32 p) {
     if (!P.sigma_layout) return p;
-    const u32 E = P.N >> 5, l = p / E, r = p % E;
-    return (r >> 2) * 128 + 4 * l + (r & 3);
+    const u32 S = P.sigma_layout == 2 ? P.N >> 1 : P.N, ps = p & (S - 1);   // 2: the two-half layout of br_quad.cuh
+    const u32 E = S >> 5, l = ps / E, r = ps % E;
+    return (p - ps) + (r >> 2) * 128 + 4 * l + (r & 3);
 }
 
 // one RGSW / automorphism-key row per CTA.  desc[blk] = {kind, exponent mm in [0, 2N) or automorphism index k, first output

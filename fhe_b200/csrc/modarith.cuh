@@ -33,12 +33,23 @@ __device__ __forceinline__ u32 reduce64(u64 x, u32 s, u32 mu, u32 Q) {
     u32 q  = __umulhi(xh, mu);
     return (u32)x - q * Q;
 }
-// The same with mu = floor(2^(s+32) / Q) of up to 34 bits (Q of 29 or 30 bits, where 2^s exceeds Q): only the low 32 bits of the
-// quotient estimate enter x - q Q mod 2^32, so the high part of mu is one more multiply-add.
+// The same with mu = floor(2^(s+32) / Q) above 32 bits (2^s > Q): only the low 32 bits of the quotient estimate enter
+// x - q Q mod 2^32, so the high part of mu is one more multiply-add.  The estimate is short by less than
+// x / 2^(s+32) + 2^s / Q + 1, so the result stays below 4Q only while that sum is at most 4: the host checks it per context
+// (29-bit Q at N = 2048: 3.0 with two digits, 3.75 with three; a 30-bit Q gives 4.0000 and takes reduce64w instead).
 __device__ __forceinline__ u32 reduce64x(u64 x, u32 s, u32 mu, u32 mu_hi, u32 Q) {
     u32 xh = (u32)(x >> s);
     u32 q  = __umulhi(xh, mu) + xh * mu_hi;
     return (u32)x - q * Q;
+}
+// Any x < 2^64 with Q < 2^30 -> [0, 4Q), for the moduli where 2^s would exceed Q and the truncated Barrett step above loses its
+// error bound (28- to 30-bit Q at N = 2048): the high word is folded with a Shoup multiplication by R = 2^32 mod Q ([0, 2Q),
+// exact for any 32-bit operand), the low word takes a 32-bit Barrett step with mu32 = floor(2^32 / Q) ([0, 2Q)).
+__device__ __forceinline__ u32 reduce64w(u64 x, u32 R, u32 Rs, u32 mu32, u32 Q) {
+    const u32 hi = (u32)(x >> 32), lo = (u32)x;
+    const u32 t = hi * R - __umulhi(hi, Rs) * Q;
+    const u32 l = lo - __umulhi(lo, mu32) * Q;
+    return t + l;
 }
 __device__ __forceinline__ u64 mad_wide(u32 a, u32 b, u64 c) {
     return (u64)a * b + c;

@@ -200,6 +200,7 @@ int luxb200_rns_plan_create(uint32_t N, uint32_t sizeQ, const uint64_t* q, uint3
         if (!rc) rc = luxb200_ntt_plan_create(N, sizeP, p, nullptr, device, &pl->nttP);
     }
     if (!rc && cudaStreamCreateWithFlags(&pl->stream, cudaStreamNonBlocking) != cudaSuccess) rc = lb_fail(LUXB200_ERR_CUDA, "stream creation failed");
+    if (!rc && cudaDeviceSynchronize() != cudaSuccess) rc = lb_fail(LUXB200_ERR_CUDA, "table upload failed");   // the uploads above have landed
     if (rc) { luxb200_rns_plan_destroy(pl); return rc; }
     *out = pl;
     return 0;
@@ -351,10 +352,14 @@ int luxb200_approx_mod_switch(luxb200_rns_plan* pl, const uint64_t* x, uint64_t*
     for (uint64_t off = 0; off < count; off += chunk) {
         const uint64_t m = std::min(chunk, count - off);
         LB_TRY(pl->stage_in.ensure(m * in_el * 8)); LB_TRY(pl->stage_out.ensure(m * out_el * 8));
-        LB_CUDA(cudaMemcpy(pl->stage_in.p, x + off * in_el, m * in_el * 8, cudaMemcpyHostToDevice));
+        // on the plan's stream and waited for: a synchronous cudaMemcpy from pageable memory may return before its DMA has landed,
+        // and the plan's non-blocking streams do not order themselves behind the default stream
+        LB_CUDA(cudaMemcpyAsync(pl->stage_in.p, x + off * in_el, m * in_el * 8, cudaMemcpyHostToDevice, pl->stream));
+        LB_CUDA(cudaStreamSynchronize(pl->stream));
         if (what) LB_TRY(luxb200_approx_mod_down_dev(pl, pl->stage_in.p, pl->stage_out.p, m));
         else LB_TRY(luxb200_approx_mod_up_dev(pl, pl->stage_in.p, pl->stage_out.p, m));
-        LB_CUDA(cudaMemcpy(out + off * out_el, pl->stage_out.p, m * out_el * 8, cudaMemcpyDeviceToHost));
+        LB_CUDA(cudaMemcpyAsync(out + off * out_el, pl->stage_out.p, m * out_el * 8, cudaMemcpyDeviceToHost, pl->stream));
+        LB_CUDA(cudaStreamSynchronize(pl->stream));
     }
     return 0;
 }

@@ -491,7 +491,15 @@ def test_wide_sets_vs_oracle(name, method, cnt):
                                               (54, 2048, 1 << 27, 1 << 35),    # 1 digit
                                               (27, 1024, 1 << 5, 1 << 14),     # logQ = 11 context: 5 digits at N = 1024
                                               (27, 1024, 1 << 14, 1 << 14),    # 1 digit at N = 1024
-                                              (45, 512, 1 << 15, 1 << 20)])    # small ring, 64-bit residues
+                                              (45, 512, 1 << 15, 1 << 20),     # small ring, 64-bit residues
+                                              # N = 2048 below 2^30: GINX / AP on the four-warp register-resident kernel
+                                              # (br_quad.cuh), one case per Q size class and digit count; LMKCDEY stays wide
+                                              (29, 2048, 1 << 10, 1 << 14),    # 2 digits, 34-bit reduction constant
+                                              (30, 2048, 1 << 10, 1 << 14),    # 4Q just below 2^32
+                                              (30, 2048, 1 << 8, 1 << 14),     # 3 digits at 30 bits
+                                              (28, 2048, 1 << 7, 1 << 14),     # 3 digits
+                                              (27, 2048, 1 << 9, 1 << 14),     # 2 digits, 27-bit Q
+                                              (25, 2048, 1 << 9, 1 << 14)])    # 25-bit Q
 def test_wide_custom_params_all_methods(method, bits, N, baseG, qKS):
     """hand-made parameter sets with a short LWE key (n = 24) so that AP (whose key grows with baseR * digitsR) is cheap:
     all three methods through the shared-memory kernel, every primitive of the path against the oracle — gates, EvalFunc,
