@@ -187,8 +187,8 @@ int luxb200_ctx_create(const luxb200_params* p, int device, luxb200_ctx** out) {
     // the register-resident warp-pair kernels cover N = 1024 with 2 or 3 digits and N = 512 with 2, Q < 2^30; everything else
     // (N = 2048, 64-bit Q, 1 / 4 / 5 digits) runs the shared-memory kernel of br_wide.cuh
     // r2: N = 2048 with 2 or 3 digits (GINX and AP) runs the same register-resident code as four warps per ciphertext
-    // (br_quad.cuh); LMKCDEY at N = 2048 (cross-half automorphism gathers) stays on br_wide.cuh
-    c->quad = p->Q < (1ull << 30) && p->Q >= (1ull << 24) && c->logN == 11 && (c->rows == 4 || c->rows == 6) && p->method != LUXB200_LMKCDEY;
+    // (br_quad.cuh)
+    c->quad = p->Q < (1ull << 30) && p->Q >= (1ull << 24) && c->logN == 11 && (c->rows == 4 || c->rows == 6);
     if (c->quad && bits_of(p->Q) < 30) {
         // below 30 bits these kernels use reduce64x, which leaves less than (xmax / 2^(s+32) + 2^s / Q + 1) Q: that must stay
         // under 4Q (it is 3.0 / 3.75 for the 29-bit sets with two / three digits); a modulus that leaves no margin runs wide
@@ -278,7 +278,8 @@ int luxb200_ctx_create(const luxb200_params* p, int device, luxb200_ctx** out) {
     if (p->method == LUXB200_LMKCDEY) {
         // EVALUATION-format automorphism maps (PrecomputeAutoMap, nbtheory2.cpp:264-275) for k = 2N-5, 5^1..5^w,
         // as gather indices in sigma order: out[sigma(p)] = in[sigma(map[p])]
-        const uint32_t N = p->N, M = 2 * N, E = N / 32, w = p->numAutoKeys;
+        const uint32_t N = p->N, M = 2 * N, w = p->numAutoKeys;
+        const uint32_t E = (c->quad ? N / 2 : N) / 32, HM = c->quad ? N / 2 - 1 : N - 1;   // quad: two halves, each in its own sigma order
         std::vector<u32> h((size_t)(w + 1) * N);
         for (uint32_t t = 0; t <= w; ++t) {
             uint32_t k = (t == 0) ? M - 5 : (uint32_t)powmod(5, t, M);
@@ -286,8 +287,8 @@ int luxb200_ctx_create(const luxb200_params* p, int device, luxb200_ctx** out) {
                 uint32_t jt = 2 * j + 1;
                 uint32_t idx = (uint32_t)(((uint64_t)jt * k) % M) >> 1;
                 uint32_t dst = bitrev(j, c->logN), src = bitrev(idx, c->logN);
-                uint32_t ld = dst / E, rd = dst % E;
-                h[(size_t)t * N + (rd >> 2) * 128 + 4 * ld + (rd & 3)] = src;  // natural EVAL index of the source
+                uint32_t ds = dst & HM, ld = ds / E, rd = ds % E;
+                h[(size_t)t * N + (dst - ds) + (rd >> 2) * 128 + 4 * ld + (rd & 3)] = src;  // natural EVAL index of the source
             }
         }
         if (c->wide.on) {   // natural order for the shared-memory kernel: out[brv(j)] = in[brv(idx)]

@@ -126,8 +126,28 @@ __device__ __forceinline__ void quad_digits(const u32 (&acc)[32], u32 (&dg)[ROWS
     }
 }
 
-// GINX = true: RingGSWAccumulatorCGGI::EvalAcc (rgsw-acc-cggi.cpp:59-68); false: the op lists of br_sched.cuh restricted to
-// external products (AP, rgsw-acc-dm.cpp:118-143, and ExternalProductBatch)
+// EVALUATION-format automorphism of one polynomial held by a warp pair (poly-impl.h:345-356): out[p] = in[map[p]], map in the
+// two-half sigma order with natural source indices 0 .. 2047
+template <int LOGH>
+__device__ __forceinline__ void quad_permute(u32 (&x)[32], u32* scr, const u32* pscr, const u32* __restrict__ map, int h, int bar, int lane) {
+    using W = WNtt<10, LOGH>;
+    __syncwarp();
+    W::store_B(scr, x, lane);
+    pair_barrier(bar);
+    const u32* half[2] = {h ? pscr : scr, h ? scr : pscr};
+#pragma unroll
+    for (int v = 0; v < 8; ++v) {
+        const uint4 s = __ldg(reinterpret_cast<const uint4*>(map) + v * 32 + lane);
+        x[4 * v]     = half[s.x >> 10][W::phys(s.x & 1023u)];
+        x[4 * v + 1] = half[s.y >> 10][W::phys(s.y & 1023u)];
+        x[4 * v + 2] = half[s.z >> 10][W::phys(s.z & 1023u)];
+        x[4 * v + 3] = half[s.w >> 10][W::phys(s.w & 1023u)];
+    }
+    pair_barrier(bar);   // both halves are read before either scratch is reused
+}
+
+// GINX = true: RingGSWAccumulatorCGGI::EvalAcc (rgsw-acc-cggi.cpp:59-68); false: the op lists of br_sched.cuh
+// (AP, rgsw-acc-dm.cpp:118-143; LMKCDEY with its automorphism rounds, rgsw-acc-lmkcdey.cpp:228-287; ExternalProductBatch)
 template <int LOGH, int ROWS, int CTS, bool GINX>
 __global__ void __launch_bounds__(128 * CTS, 1) br_quad_kernel(const __grid_constant__ QuadParams P) {
     using W = WNtt<10, LOGH>;
@@ -221,12 +241,22 @@ __global__ void __launch_bounds__(128 * CTS, 1) br_quad_kernel(const __grid_cons
             if ((op & OP_MASK) == OP_END) done = true;
             op_next = done ? (u32)OP_END : ops[pc + 1];
             if (__syncthreads_and(done)) break;
-            const bool ext = !done && (op & OP_MASK) == OP_EXT;
-            const u32 arg  = op & ~OP_MASK;
+            const u32 ty = done ? (u32)OP_END : (op & OP_MASK), arg = op & ~OP_MASK;
             u32 dg[ROWS / 2][32];
-            if (ext) quad_digits<LOGH, ROWS, false>(acc, dg, P, C, scr, pscr, twB, twiB, exs, c, h, bar, lane);
+            if (ty == OP_AUTO || (ty == OP_PERM1 && c == 1))
+                quad_permute<LOGH>(acc, scr, pscr, P.B.automap + (size_t)arg * NP + 1024 * h, h, bar, lane);
+            // external product: every warp; automorphism: only component 0 is key-switched (one inlined copy of the pipeline)
+            if (ty == OP_EXT || (ty == OP_AUTO && c == 0))
+                quad_digits<LOGH, ROWS, false>(acc, dg, P, C, scr, pscr, twB, twiB, exs, c, h, bar, lane);
             __syncthreads();
-            if (ext) mac_replace<10, ROWS, NP, XRED>(acc, dg, exs + 256 * h, P.B, P.B.bsk + (size_t)arg * kblock + 1024 * h, c, lane);
+            if (ty == OP_EXT) {
+                mac_replace<10, ROWS, NP, XRED>(acc, dg, exs + 256 * h, P.B, P.B.bsk + (size_t)arg * kblock + 1024 * h, c, lane);
+            } else if (ty == OP_AUTO) {
+                constexpr int ND = ROWS / 2;
+                const u32* ak = P.B.bsk + P.B.auto_off + (size_t)arg * ((size_t)ND * 2 * NP) + 1024 * h;
+                if (c == 0) mac_auto_split<10, ND, 0, ND, false, NP, XRED>(acc, dg, exs + 256 * h, P.B, ak, 0, lane);
+                else        mac_auto_split<10, ND, 0, 0, true, NP, XRED>(acc, dg, exs + 256 * h, P.B, ak, 1, lane);
+            }
             if (!done) ++pc;
         }
     }

@@ -96,7 +96,7 @@ __device__ __forceinline__ void permute_eval(u32 (&x)[(1 << LOGN) / 32], u32* sc
 }
 
 // acc[c] (+)= sum_d dig[d] * ak[d][c]; digits LO <= d < HI are this warp's own (registers), the others come from exch
-template <int LOGN, int ND, int LO, int HI, bool ADD>
+template <int LOGN, int ND, int LO, int HI, bool ADD, int RS = (1 << LOGN), int RED = 0>
 __device__ __forceinline__ void mac_auto_split(u32 (&acc)[(1 << LOGN) / 32], const u32 (&dg)[ND][(1 << LOGN) / 32],
                                                const uint4* exch, const BrParams& P, const u32* ak, int c, int lane) {
     constexpr int N = 1 << LOGN, E = N / 32;
@@ -106,8 +106,8 @@ __device__ __forceinline__ void mac_auto_split(u32 (&acc)[(1 << LOGN) / 32], con
         uint4 k1[ND], dx[ND];
 #pragma unroll
         for (int d = 0; d < ND; ++d) {
-            k1[d] = __ldg(reinterpret_cast<const uint4*>(ak + (size_t)(d * 2 + c) * N) + v * 32 + lane);
-            if (d < LO || d >= HI) dx[d] = exch[2 * d * (N / 4) + v * 32 + lane];   // warp 0 publishes digit d in row 2d
+            k1[d] = __ldg(reinterpret_cast<const uint4*>(ak + (size_t)(d * 2 + c) * RS) + v * 32 + lane);
+            if (d < LO || d >= HI) dx[d] = exch[2 * d * (RS / 4) + v * 32 + lane];   // warp 0 publishes digit d in row 2d
         }
 #pragma unroll
         for (int e = 0; e < 4; ++e) {
@@ -115,7 +115,7 @@ __device__ __forceinline__ void mac_auto_split(u32 (&acc)[(1 << LOGN) / 32], con
 #pragma unroll
             for (int d = 0; d < ND; ++d)
                 s = mad_wide((d >= LO && d < HI) ? dg[d][4 * v + e] : comp4(dx[d], e), comp4(k1[d], e), s);
-            acc[4 * v + e] = csub(red64<0>(s, P, Q), Q2);
+            acc[4 * v + e] = csub(red64<RED>(s, P, Q), Q2);
         }
     }
 }

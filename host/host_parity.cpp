@@ -146,6 +146,10 @@ int main(int argc, char** argv) {
     else if (set == "STD128_3") ps = STD128_3;          // baseG = 128: digitsG - 1 = 3
     else if (set == "STD128Q") ps = STD128Q;
     else if (set == "STD128_4_LMKCDEY") { ps = STD128_4_LMKCDEY; method = LMKCDEY; }
+    else if (set == "STD256") ps = STD256;              // N = 2048, 29-bit Q, 2 digits: the four-warp kernel (br_quad.cuh)
+    else if (set == "STD256_3") ps = STD256_3;          // 3 digits
+    else if (set == "STD256_LMKCDEY") { ps = STD256_LMKCDEY; method = LMKCDEY; }   // 30-bit Q: the shared-memory kernel
+    else if (set == "STD192") ps = STD192;              // 37-bit Q: 64-bit residues
 
     BinFHEContext cc;
     cc.GenerateBinFHEContext(ps, method);
