@@ -38,11 +38,17 @@ struct QuadSmem {
 // before its next use of the scratch)
 template <bool TWO>
 __device__ __forceinline__ void quad_swap(const u32 (&mine)[32], u32 (&other)[32], u32* scr, const u32* pscr, int bar, int lane) {
+    // any (register, lane) -> word mapping works as long as both warps use the same one: 16-byte vectors, conflict-free
+    uint4* w4 = reinterpret_cast<uint4*>(scr);
+    const uint4* r4 = reinterpret_cast<const uint4*>(pscr);
 #pragma unroll
-    for (int r = 0; r < 32; ++r) scr[32 * r + lane] = mine[r];
+    for (int v = 0; v < 8; ++v) w4[v * 32 + lane] = make_uint4(mine[4 * v], mine[4 * v + 1], mine[4 * v + 2], mine[4 * v + 3]);
     pair_barrier(bar);
 #pragma unroll
-    for (int r = 0; r < 32; ++r) other[r] = pscr[32 * r + lane];
+    for (int v = 0; v < 8; ++v) {
+        const uint4 t = r4[v * 32 + lane];
+        other[4 * v] = t.x; other[4 * v + 1] = t.y; other[4 * v + 2] = t.z; other[4 * v + 3] = t.w;
+    }
     if (TWO) pair_barrier(bar);
 }
 
@@ -98,14 +104,19 @@ __device__ __forceinline__ void quad_digits(const u32 (&acc)[32], u32 (&dg)[ROWS
 #pragma unroll
     for (int k = 0; k < ND; ++k)
 #pragma unroll
-        for (int r = 0; r < 32; ++r) myrow[k][32 * r + lane] = dg[k][r];
+        for (int v = 0; v < 8; ++v)
+            reinterpret_cast<uint4*>(myrow[k])[v * 32 + lane] = make_uint4(dg[k][4 * v], dg[k][4 * v + 1], dg[k][4 * v + 2], dg[k][4 * v + 3]);
     pair_barrier(bar);
 #pragma unroll
     for (int k = 0; k < ND; ++k)
 #pragma unroll
-        for (int r = 0; r < 32; ++r) {
-            const u32 o = prow[k][32 * r + lane];
-            dg[k][r] = h ? o + Q2 - dg[k][r] : dg[k][r] + o;   // a - w b + 2Q | a + w b : below 3Q
+        for (int v = 0; v < 8; ++v) {
+            const uint4 t = reinterpret_cast<const uint4*>(prow[k])[v * 32 + lane];
+#pragma unroll
+            for (int e = 0; e < 4; ++e) {
+                const u32 o = comp4(t, e);
+                dg[k][4 * v + e] = h ? o + Q2 - dg[k][4 * v + e] : dg[k][4 * v + e] + o;   // a - w b + 2Q | a + w b : below 3Q
+            }
         }
     pair_barrier(bar);   // both halves are read before either is overwritten (transpose scratch of polynomial k >= 1, publish)
     if (MULTI) {

@@ -9,6 +9,9 @@
 //                makes: reference containers in, reference containers out) and print e2e_cpp
 //   --dcrt       also check host/dcrt_b200 against DCRTPoly::SwitchFormat at N = 2^16, 32 limbs of 60 bits
 #include <cstdio>
+#include <execinfo.h>
+#include <csignal>
+#include <unistd.h>
 #include <cstdlib>
 #include <functional>
 #include <random>
@@ -120,7 +123,20 @@ static void dcrt_check(uint32_t N, uint32_t L, uint32_t bits, size_t count) {
                 t2 - t1);
 }
 
+// a crash of the acceptance program names its frames on stderr instead of dying silently (stdout is a pipe under pytest)
+static void on_fatal_signal(int sig) {
+    void* bt[64];
+    const int nbt = backtrace(bt, 64);
+    std::fprintf(stderr, "host_parity: fatal signal %d\n", sig);
+    backtrace_symbols_fd(bt, nbt, 2);
+    _exit(128 + sig);
+}
+
 int main(int argc, char** argv) {
+    std::signal(SIGSEGV, on_fatal_signal);
+    std::signal(SIGABRT, on_fatal_signal);
+    std::signal(SIGBUS, on_fatal_signal);
+    std::setvbuf(stdout, nullptr, _IOLBF, 0);
     std::vector<std::string> pos;
     size_t n_dev = 1, e2e_gates = 0;
     bool dcrt = false, gpu_keygen = false;
@@ -175,6 +191,11 @@ int main(int argc, char** argv) {
         m1[i] = rng() & 1; m2[i] = rng() & 1; m3[i] = rng() & 1;
         c1[i] = cc.Encrypt(sk, m1[i]); c2[i] = cc.Encrypt(sk, m2[i]); c3[i] = cc.Encrypt(sk, m3[i]);
     }
+    // The reference fills its static NTT twiddle tables on first use, without a lock (ChineseRemainderTransformFTTNat::
+    // ForwardTransformToBitReverseInPlace -> PreCompute).  cc.BTKeyGen does that as a side effect; with --gpu-keygen no
+    // reference transform has run yet, and the OpenMP loops below would race on the first one (1 crash in 60 runs of
+    // TOY_LMKCDEY inside the reference's SwitchFormat).  One serial gate fills the tables for this ring.
+    if (cnt) (void)cc.EvalBinGate(AND, c1[0], c2[0]);
 
     // ---- seam 2: batch API vs the reference's per-ciphertext calls ---------------------------------------------
     for (BINGATE g : {AND, OR, NAND, NOR, XOR, XNOR}) {
