@@ -188,7 +188,7 @@ int luxb200_ctx_create(const luxb200_params* p, int device, luxb200_ctx** out) {
     // (N = 2048, 64-bit Q, 1 / 4 / 5 digits) runs the shared-memory kernel of br_wide.cuh
     // r2: N = 2048 with 2 or 3 digits (GINX and AP) runs the same register-resident code as four warps per ciphertext
     // (br_quad.cuh)
-    c->quad = p->Q < (1ull << 30) && p->Q >= (1ull << 24) && c->logN == 11 && (c->rows == 4 || c->rows == 6);
+    c->quad = p->Q < (1ull << 30) && p->Q >= (1ull << 24) && c->logN == 11 && (c->rows == 4 || c->rows == 6 || (c->rows == 8 && p->Q < (1ull << 27)));
     if (c->quad && bits_of(p->Q) < 30) {
         // below 30 bits these kernels use reduce64x, which leaves less than (xmax / 2^(s+32) + 2^s / Q + 1) Q: that must stay
         // under 4Q (it is 3.0 / 3.75 for the 29-bit sets with two / three digits); a modulus that leaves no margin runs wide

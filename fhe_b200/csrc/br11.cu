@@ -8,7 +8,7 @@ namespace {
 
 template <int LOGH, int ROWS>
 int launch_quad_t(luxb200_ctx* c, const BrParams& B, int sched_only) {
-    constexpr int CTS = ROWS > 4 ? 2 : 3;   // 12 warps at 168 registers, 8 with three digits (like the N = 1024 kernels)
+    constexpr int CTS = ROWS > 4 ? 2 : 3;   // 12 warps at 168 registers, 8 with three or four digits (like the N = 1024 kernels)
     using S = QuadSmem<LOGH, ROWS, CTS>;
     static_assert(sizeof(S) <= 232448, "quad shared memory exceeds the 227 KB opt-in limit");
     QuadParams P;
@@ -46,6 +46,7 @@ int lb_launch_quad(luxb200_ctx* c, const BrParams& B, int sched_only) {
         case 46: return launch_quad_t<4, 6>(c, B, sched_only);
         case 36: return launch_quad_t<3, 6>(c, B, sched_only);   // STD256_3, STD256_4 (29)
         case 26: return launch_quad_t<2, 6>(c, B, sched_only);
+        case 58: return launch_quad_t<5, 8>(c, B, sched_only);   // four digits below 2^27: STD256Q_3, STD256Q_4, STD256Q_4_LMKCDEY
         default:
             return lb_fail(LUXB200_ERR_UNSUPPORTED, "no N = 2048 blind-rotation kernel for a %u-bit Q with %u digit rows", 32 - c->ntt.logH, c->rows);
     }

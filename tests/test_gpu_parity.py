@@ -499,7 +499,8 @@ def test_wide_sets_vs_oracle(name, method, cnt):
                                               (30, 2048, 1 << 8, 1 << 14),     # 3 digits at 30 bits
                                               (28, 2048, 1 << 7, 1 << 14),     # 3 digits
                                               (27, 2048, 1 << 9, 1 << 14),     # 2 digits, 27-bit Q
-                                              (25, 2048, 1 << 9, 1 << 14)])    # 25-bit Q
+                                              (25, 2048, 1 << 9, 1 << 14),     # 25-bit Q
+                                              (26, 2048, 1 << 6, 1 << 14)])    # 4 digits (8 digit rows), like STD256Q_3 / _4
 def test_wide_custom_params_all_methods(method, bits, N, baseG, qKS):
     """hand-made parameter sets with a short LWE key (n = 24) so that AP (whose key grows with baseR * digitsR) is cheap:
     all three methods through the shared-memory kernel, every primitive of the path against the oracle — gates, EvalFunc,

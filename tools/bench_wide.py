@@ -13,7 +13,7 @@ from fhe_b200.context import BinFHEContext  # noqa: E402
 
 G = int(sys.argv[1]) if len(sys.argv) > 1 else 1184
 rng = np.random.default_rng(1)
-for name, method in [("STD256", "GINX"), ("STD256_3", "GINX"), ("STD192", "GINX"), ("STD192Q_3", "GINX"), ("STD128Q_3", "GINX"),
+for name, method in [("STD256", "GINX"), ("STD256_3", "GINX"), ("STD256Q_3", "GINX"), ("STD192", "GINX"), ("STD192Q_3", "GINX"), ("STD128Q_3", "GINX"),
                      ("STD192_LMKCDEY", "LMKCDEY"), ("STD256_LMKCDEY", "LMKCDEY")]:
     ctx = BinFHEContext().GenerateBinFHEContext(name, method)
     bsk = rng.integers(0, ctx.Q, size=ctx.bsk_len(), dtype=np.uint64)
