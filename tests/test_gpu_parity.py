@@ -551,6 +551,29 @@ def test_wide_custom_params_all_methods(method, bits, N, baseG, qKS):
     ctx.close(); oc.close()
 
 
+def test_n2048_pipelined_host_path_matches_small_batches():
+    """N = 2048 (STD256, the four-warp kernel) at a batch large enough for the three-stream pipelined host path (>= 32 768
+    gates): every output equals what the same ciphertexts give in small, unpipelined calls — batch position, chunking and the
+    copy overlap change nothing — and the device-generated keys decrypt every gate to its truth table."""
+    from fhe_b200.context import BinFHEContext
+    from fhe_b200 import keygen as kg
+    ctx = BinFHEContext().GenerateBinFHEContext("STD256", "GINX")
+    rng = np.random.default_rng(256)
+    sk = rng.integers(-1, 2, size=ctx.n).astype(np.int64)
+    ctx.BTKeyGen(sk, seed=77)   # keys drawn on the device (tests/…::test_device_btkeygen checks them against the oracle)
+    G = 33000
+    m1 = rng.integers(0, 2, G); m2 = rng.integers(0, 2, G)
+    a1, b1 = kg.encrypt(ctx, sk, m1, rng); a2, b2 = kg.encrypt(ctx, sk, m2, rng)
+    (oa, ob), res = ctx.EvalBinGateBatch("NAND", (a1, b1), (a2, b2))
+    assert res.success, res.error
+    assert (kg.decrypt(ctx, sk, oa, ob) == 1 - (m1 & m2)).all()
+    for lo, hi in ((0, 700), (15984 - 300, 15984 + 300), (G - 901, G)):   # first chunk, a chunk boundary, the tail
+        (pa, pb), res = ctx.EvalBinGateBatch("NAND", (a1[lo:hi], b1[lo:hi]), (a2[lo:hi], b2[lo:hi]))
+        assert res.success, res.error
+        assert (pa == oa[lo:hi]).all() and (pb == ob[lo:hi]).all(), (lo, hi)
+    ctx.close()
+
+
 # ---- key-ordered key switch (ks_tile.cuh): the 16-bit keys of the qKS = 2^14, baseKS = 32 sets ---------------------------------
 @pytest.mark.parametrize("n,N,method,cnt", [(503, 1024, "GINX", 700), (447, 1024, "LMKCDEY", 257), (40, 512, "GINX", 1000)])
 def test_keyswitch_tile_vs_oracle_and_gather_kernel(n, N, method, cnt, monkeypatch):
