@@ -60,8 +60,8 @@ def _run_parity(args, timeout=1500):
 @pytest.mark.parametrize("pset,cnt,pairs", [("TOY", 12, 2), ("TOY_AP", 12, 1), ("TOY_LMKCDEY", 12, 1), ("STD128", 9, 2),
                                             ("STD128_LMKCDEY", 6, 1), ("STD128_3", 6, 1), ("STD128_4_LMKCDEY", 6, 1),
                                             ("STD128_AP", 4, 1),    # STD128_AP: the reference's own 1 GB refresh key
-                                            ("STD256", 4, 0), ("STD256_3", 3, 0),   # N = 2048: four warps per ciphertext
-                                            ("STD256_LMKCDEY", 3, 0), ("STD192", 3, 0)])   # shared-memory kernel, u32 / u64
+                                            ("STD256", 2, 0), ("STD256_3", 2, 0),   # N = 2048: four warps per ciphertext,
+                                            ("STD256_LMKCDEY", 2, 0), ("STD192", 2, 0)])   # and the shared-memory kernel (64-bit Q)
 def test_host_layer_matches_reference(pset, cnt, pairs):
     _run_parity([pset, cnt, pairs])
 
