@@ -1,6 +1,6 @@
-// br11.cu — N = 2048 on the register-resident code: four warps per ciphertext (br_quad.cuh).  A translation unit of its own so
-// that it compiles beside api.cu.  Sets: STD256 / STD256_3 / STD256_4 / STD256Q (GINX, AP) and hand-made sets with a Q below 2^30
-// and 2 or 3 gadget digits.
+// br11.cu — N = 2048 (log2 N = 11) on the register-resident code: four warps per ciphertext (br_quad.cuh).  A translation unit of
+// its own so that it compiles beside api.cu.  Sets: every STD256* / STD256Q* name (GINX, AP, LMKCDEY) and hand-made sets with a Q
+// below 2^30 and 2 to 4 gadget digits.
 #include "api_common.h"
 #include "br_quad.cuh"
 

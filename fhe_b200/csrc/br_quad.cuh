@@ -1,7 +1,8 @@
-// br_quad.cuh — register-resident blind rotation at N = 2048 (GINX and AP, Q < 2^30, 2 or 3 gadget digits): one ciphertext =
+// br_quad.cuh — register-resident blind rotation at N = 2048 (GINX, AP, LMKCDEY; Q < 2^30; 2 to 4 gadget digits): one ciphertext =
 // FOUR warps.  Warp (c, h) owns half h (coefficients / evaluation points 1024 h .. 1024 h + 1023) of accumulator component c,
 // 32 values per lane like the N = 1024 kernels of br_kernels.cuh, so the step body keeps their code size and register budget
-// (br11.cu's 64-values-per-lane form does not fit the instruction caches: 0.32 of the IMAD peak against 0.67).
+// (an earlier form with one warp per polynomial and 64 values per lane — 255 registers, a 10 k-instruction step body that did
+// not fit the instruction caches — reached 0.32 of the IMAD peak; this one 0.46).
 //
 // The in-place Cooley-Tukey transform of the reference (transformnat-impl.h:327-351) on 2048 points is ONE stage across the
 // two halves — (x[k], x[k+1024]) -> (x[k] + w x[k+1024], x[k] - w x[k+1024]), w = table[1] — followed by two independent
