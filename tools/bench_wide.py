@@ -11,9 +11,10 @@ ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 from fhe_b200.context import BinFHEContext  # noqa: E402
 
-G = int(sys.argv[1]) if len(sys.argv) > 1 else 1184
+G = int(sys.argv[1]) if len(sys.argv) > 1 and sys.argv[1].isdigit() else 1184
 rng = np.random.default_rng(1)
-for name, method in [("STD256", "GINX"), ("STD256_3", "GINX"), ("STD256Q_3", "GINX"), ("STD192", "GINX"), ("STD192Q_3", "GINX"), ("STD128Q_3", "GINX"),
+SETS = [("STD128_3", "GINX"), ("STD128Q", "GINX"), ("STD128_4_LMKCDEY", "LMKCDEY")] if "--n1024" in sys.argv else None
+for name, method in SETS or [("STD256", "GINX"), ("STD256_3", "GINX"), ("STD256Q_3", "GINX"), ("STD192", "GINX"), ("STD192Q_3", "GINX"), ("STD128Q_3", "GINX"),
                      ("STD192_LMKCDEY", "LMKCDEY"), ("STD256_LMKCDEY", "LMKCDEY")]:
     ctx = BinFHEContext().GenerateBinFHEContext(name, method)
     bsk = rng.integers(0, ctx.Q, size=ctx.bsk_len(), dtype=np.uint64)
