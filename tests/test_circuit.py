@@ -52,7 +52,8 @@ def oracle_circuit(oc, q, gates, in_a, in_b):
 
 @pytest.mark.gpu
 @pytest.mark.parametrize("name,method,n_gates,cnt", [("TOY", "GINX", 40, 5), ("TOY", "AP", 16, 3), ("TOY", "LMKCDEY", 16, 3),
-                                                     ("STD128", "GINX", 10, 2)])
+                                                     ("STD128", "GINX", 10, 2),
+                                                     ("STD256", "GINX", 6, 2)])   # N = 2048: the four-warp kernel under the scheduler
 def test_circuit_vs_oracle_every_wire(name, method, n_gates, cnt):
     from fhe_b200.context import BinFHEContext
     ctx = BinFHEContext().GenerateBinFHEContext(name, method)
