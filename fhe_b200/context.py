@@ -440,10 +440,11 @@ class RNSPlan:
         _l.check(self.L.luxb200_approx_mod_switch(self.h, _l.ptr(x), _l.ptr(out), x.shape[0], 0))
         return out
 
-    def ApproxModDown(self, x):
+    def ApproxModDown(self, x, t=0):
+        """t = 0: CKKS; t > 0: the BGV branch with plaintext modulus t (dcrtpoly-impl.h:1003-1005, :1021-1023)."""
         x = np.ascontiguousarray(x, np.uint64)
         out = np.empty((x.shape[0], len(self.q), self.N), np.uint64)
-        _l.check(self.L.luxb200_approx_mod_switch(self.h, _l.ptr(x), _l.ptr(out), x.shape[0], 1))
+        _l.check(self.L.luxb200_approx_mod_switch_bgv(self.h, _l.ptr(x), _l.ptr(out), x.shape[0], 1, int(t)))
         return out
 
     def close(self):

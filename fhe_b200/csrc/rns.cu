@@ -76,6 +76,18 @@ __global__ void rns_moddown_tail_kernel(const u64* __restrict__ x, u32 x_stride,
     out[gid] = r >= qi ? r - qi : r;
 }
 
+// data[c][l][k] <- data[c][l][k] * w_l mod m_l (canonical in, canonical out): the BGV factors of ApproxModDown, t^-1 mod p_j on the
+// P part before the basis switch and t mod q_i on the switched part (dcrtpoly-impl.h:1003-1005, :1021-1023)
+__global__ void rns_scale_limbs_kernel(u64* __restrict__ data, const u64* __restrict__ mod, const u64* __restrict__ w,
+                                       const u64* __restrict__ ws, u32 limbs, u32 N, u64 count) {
+    const u64 gid = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (gid >= count * limbs * N) return;
+    const u32 l = (u32)((gid / N) % limbs);
+    const u64 m = mod[l], v = data[gid];
+    const u64 r = v * w[l] - __umul64hi(v, ws[l]) * m;
+    data[gid] = r >= m ? r - m : r;
+}
+
 __global__ void rns_copy_limbs_kernel(const u64* __restrict__ in, u32 in_stride, u32 in_off, u64* __restrict__ out, u32 out_stride,
                                       u32 out_off, u32 limbs, u32 N, u64 count) {
     const u64 gid = (u64)blockIdx.x * blockDim.x + threadIdx.x;
@@ -123,7 +135,9 @@ struct luxb200_rns_plan {
     int device = 0;
     Tables up, down;            // Q -> P (mod up) and P -> Q (mod down)
     std::vector<u64> pinv, pinv_s;   // P^-1 mod q_i
-    DevBuf dev_up, dev_down, dev_tail, tmpP, tmpQ, stage_in, stage_out;
+    DevBuf dev_up, dev_down, dev_tail, tmpP, tmpQ, stage_in, stage_out, dev_t;
+    uint64_t t_cached = 0;            // plaintext modulus whose BGV factors are resident in dev_t
+    std::vector<u64> t_host;          // [p | tinv | tinv_s | q | tq | tq_s]
     RnsDev d_up{}, d_down{};
     const u64 *d_q = nullptr, *d_pinv = nullptr, *d_pinv_s = nullptr;
     luxb200_ntt_plan *nttQ = nullptr, *nttP = nullptr;
@@ -261,8 +275,12 @@ int luxb200_approx_mod_up_dev(luxb200_rns_plan* pl, const void* x_dev, void* out
     return 0;
 }
 
-// ApproxModDown (t = 0): x [count][sizeQ + sizeP][N] EVALUATION -> out [count][sizeQ][N] EVALUATION
+// ApproxModDown (t = 0, CKKS): x [count][sizeQ + sizeP][N] EVALUATION -> out [count][sizeQ][N] EVALUATION
 int luxb200_approx_mod_down_dev(luxb200_rns_plan* pl, const void* x_dev, void* out_dev, uint64_t count) {
+    return luxb200_approx_mod_down_bgv_dev(pl, x_dev, out_dev, count, 0);
+}
+// ApproxModDown with plaintext modulus t (BGV): the P part times t^-1 mod p_j before the switch, the switched part times t mod q_i
+int luxb200_approx_mod_down_bgv_dev(luxb200_rns_plan* pl, const void* x_dev, void* out_dev, uint64_t count, uint64_t t) {
     if (!pl || !x_dev || !out_dev) return lb_fail(LUXB200_ERR_INVALID_ARG, "null argument");
     if (!pl->nttQ) return lb_fail(LUXB200_ERR_UNSUPPORTED, "this plan has no NTT (N or the moduli do not admit one)");
     if (count == 0) return 0;
@@ -271,11 +289,36 @@ int luxb200_approx_mod_down_dev(luxb200_rns_plan* pl, const void* x_dev, void* o
     const u64* x = reinterpret_cast<const u64*>(x_dev);
     u64* out = reinterpret_cast<u64*>(out_dev);
     LB_TRY(pl->tmpQ.ensure(count * sq * N * 8)); LB_TRY(pl->tmpP.ensure(count * sp * N * 8));
+    const u64 *d_tp = nullptr, *d_tq = nullptr;
+    if (t) {
+        if (pl->t_cached != t) {
+            std::vector<u64>& h = pl->t_host;
+            h.assign(3 * (size_t)(sq + sp), 0);
+            for (uint32_t j = 0; j < sp; ++j) {
+                const u64 m = pl->up.p[j];
+                if (t % m == 0) return lb_fail(LUXB200_ERR_INVALID_ARG, "t has no inverse modulo an auxiliary prime");
+                const u64 inv = lb::invmod_prime(t % m, m);
+                h[j] = m; h[sp + j] = inv; h[2 * sp + j] = lb::shoup64(inv, m);
+            }
+            for (uint32_t i = 0; i < sq; ++i) {
+                const u64 m = pl->up.q[i];
+                h[3 * sp + i] = m; h[3 * sp + sq + i] = t % m; h[3 * sp + 2 * sq + i] = lb::shoup64(t % m, m);
+            }
+            LB_TRY(pl->dev_t.ensure(h.size() * 8));
+            LB_CUDA(cudaMemcpyAsync(pl->dev_t.p, h.data(), h.size() * 8, cudaMemcpyHostToDevice, pl->stream));
+            LB_CUDA(cudaStreamSynchronize(pl->stream));
+            pl->t_cached = t;
+        }
+        d_tp = pl->dev_t.as<u64>(); d_tq = d_tp + 3 * sp;
+    }
     rns_copy_limbs_kernel<<<nblk(count * sp * N, 256), 256, 0, pl->stream>>>(x, sq + sp, sq, pl->tmpP.as<u64>(), sp, 0, sp, N, count);
     LB_CUDA(cudaStreamSynchronize(pl->stream));
     LB_TRY(luxb200_ntt_batch_dev(pl->nttP, pl->tmpP.p, count, 1, 8));
     LB_TRY(luxb200_ntt_plan_sync(pl->nttP));
+    if (t) rns_scale_limbs_kernel<<<nblk(count * sp * N, 256), 256, 0, pl->stream>>>(pl->tmpP.as<u64>(), d_tp, d_tp + sp, d_tp + 2 * sp, sp, N, count);
     LB_TRY(launch_switch(pl, pl->d_down, pl->tmpP.as<u64>(), sp, 0, pl->tmpQ.as<u64>(), sq, 0, count));
+    if (t) rns_scale_limbs_kernel<<<nblk(count * sq * N, 256), 256, 0, pl->stream>>>(pl->tmpQ.as<u64>(), d_tq, d_tq + sq, d_tq + 2 * sq, sq, N, count);
+    LB_CUDA(cudaGetLastError());
     LB_CUDA(cudaStreamSynchronize(pl->stream));
     LB_TRY(luxb200_ntt_batch_dev(pl->nttQ, pl->tmpQ.p, count, 0, 8));
     LB_TRY(luxb200_ntt_plan_sync(pl->nttQ));
@@ -343,6 +386,9 @@ int luxb200_approx_switch_crt_basis_static(luxb200_rns_plan* pl, const uint64_t*
 
 // host-buffer wrappers of the two composites (what = 0 mod up, 1 mod down)
 int luxb200_approx_mod_switch(luxb200_rns_plan* pl, const uint64_t* x, uint64_t* out, uint64_t count, int what) {
+    return luxb200_approx_mod_switch_bgv(pl, x, out, count, what, 0);
+}
+int luxb200_approx_mod_switch_bgv(luxb200_rns_plan* pl, const uint64_t* x, uint64_t* out, uint64_t count, int what, uint64_t t) {
     if (!pl || !x || !out) return lb_fail(LUXB200_ERR_INVALID_ARG, "null argument");
     if (count == 0) return 0;
     LB_TRY(lb_set_device(pl->device));
@@ -356,7 +402,7 @@ int luxb200_approx_mod_switch(luxb200_rns_plan* pl, const uint64_t* x, uint64_t*
         // and the plan's non-blocking streams do not order themselves behind the default stream
         LB_CUDA(cudaMemcpyAsync(pl->stage_in.p, x + off * in_el, m * in_el * 8, cudaMemcpyHostToDevice, pl->stream));
         LB_CUDA(cudaStreamSynchronize(pl->stream));
-        if (what) LB_TRY(luxb200_approx_mod_down_dev(pl, pl->stage_in.p, pl->stage_out.p, m));
+        if (what) LB_TRY(luxb200_approx_mod_down_bgv_dev(pl, pl->stage_in.p, pl->stage_out.p, m, t));
         else LB_TRY(luxb200_approx_mod_up_dev(pl, pl->stage_in.p, pl->stage_out.p, m));
         LB_CUDA(cudaMemcpyAsync(out + off * out_el, pl->stage_out.p, m * out_el * 8, cudaMemcpyDeviceToHost, pl->stream));
         LB_CUDA(cudaStreamSynchronize(pl->stream));

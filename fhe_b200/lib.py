@@ -81,6 +81,8 @@ SIGNATURES = {
     "luxb200_approx_mod_switch": (INT, [VP, VP, VP, U64, INT]),
     "luxb200_approx_mod_up_dev": (INT, [VP, VP, VP, U64]),
     "luxb200_approx_mod_down_dev": (INT, [VP, VP, VP, U64]),
+    "luxb200_approx_mod_switch_bgv": (INT, [VP, VP, VP, U64, INT, U64]),
+    "luxb200_approx_mod_down_bgv_dev": (INT, [VP, VP, VP, U64, U64]),
     "luxb200_evalbingate_batch_dev": (INT, [VP, INT, VP, VP, VP, VP, VP, VP, U64]),
     "luxb200_circuit_batch": (INT, [VP, U32, VP, U32, VP, U32, VP, VP, VP, VP, U64]),
     "luxb200_circuit_batch_ex": (INT, [VP, U32, VP, U32, VP, U32, VP, U32, U64, VP, VP, VP, VP, U64]),

@@ -203,6 +203,12 @@ int luxb200_approx_switch_crt_basis(luxb200_rns_plan* plan, const uint64_t* x, u
 int luxb200_approx_mod_switch(luxb200_rns_plan* plan, const uint64_t* x, uint64_t* out, uint64_t count, int what);
 int luxb200_approx_mod_up_dev(luxb200_rns_plan* plan, const void* x_dev, void* out_dev, uint64_t count);
 int luxb200_approx_mod_down_dev(luxb200_rns_plan* plan, const void* x_dev, void* out_dev, uint64_t count);
+/* The BGV branch of DCRTPolyImpl::ApproxModDown (t > 0, dcrtpoly-impl.h:1003-1005 and :1021-1023 with tInvModp / tModqPrecon of
+ * src/pke/lib/scheme/bgvrns/bgvrns-cryptoparameters.cpp:78-95): the P part is multiplied by t^-1 mod p_j before the basis switch
+ * and the switched part by t mod q_i before its NTT.  t = 0 is the CKKS form above; `what` as in luxb200_approx_mod_switch
+ * (t is ignored for what = 0). */
+int luxb200_approx_mod_switch_bgv(luxb200_rns_plan* plan, const uint64_t* x, uint64_t* out, uint64_t count, int what, uint64_t t);
+int luxb200_approx_mod_down_bgv_dev(luxb200_rns_plan* plan, const void* x_dev, void* out_dev, uint64_t count, uint64_t t);
 /* Allocation-free variant of luxb200_approx_switch_crt_basis.  It has no counterpart in the reference and was added
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
  * harnesses that forbid it).  Same arguments, same result; the device staging of the basis-switch kernel is a static device

@@ -931,19 +931,28 @@ int orc_approx_mod_up(u32 N, u32 sizeQ, const u64* q, u32 sizeP, const u64* p, c
     free(t); free(s);
     return 0;
 }
-/* ApproxModDown with t = 0 (:988-1030): EVALUATION x over Q u P -> (x_i - Switch_{P->Q}(x_P)_i) P^-1 mod q_i */
-int orc_approx_mod_down(u32 N, u32 sizeQ, const u64* q, u32 sizeP, const u64* p, const u64* x, u64* out, u64 count) {
+/* ApproxModDown (:988-1030): EVALUATION x over Q u P -> (x_i - Switch_{P->Q}(x_P)_i) P^-1 mod q_i.  ptm = 0: CKKS; ptm > 0
+ * (BGV, plaintext modulus t): the P part is multiplied by t^-1 mod p_j before the basis switch (:1003-1005, tInvModp =
+ * t.ModInverse(p_j), bgvrns-cryptoparameters.cpp:78-83) and the switched part by t mod q_i before its NTT (:1021-1023) */
+int orc_approx_mod_down_t(u32 N, u32 sizeQ, const u64* q, u32 sizeP, const u64* p, const u64* x, u64* out, u64 count, u64 ptm) {
     u64* t = malloc(sizeof(u64) * count * sizeP * N);
     u64* s = malloc(sizeof(u64) * count * sizeQ * N);
     for (u64 c = 0; c < count; ++c)
         for (u32 j = 0; j < sizeP; ++j) {
-            memcpy(t + (c * sizeP + j) * N, x + (c * (sizeQ + sizeP) + sizeQ + j) * N, sizeof(u64) * N);
-            orc_ntt(p[j], orc_root_of_unity(2 * (u64)N, p[j]), N, t + (c * sizeP + j) * N, 1, 1, 1);
+            u64* tj = t + (c * sizeP + j) * N;
+            memcpy(tj, x + (c * (sizeQ + sizeP) + sizeQ + j) * N, sizeof(u64) * N);
+            orc_ntt(p[j], orc_root_of_unity(2 * (u64)N, p[j]), N, tj, 1, 1, 1);
+            if (ptm > 0) {
+                const u64 tinv = invmod(ptm % p[j], p[j]);
+                for (u32 k = 0; k < N; ++k) tj[k] = mulmod(tj[k], tinv, p[j]);
+            }
         }
     orc_approx_switch_crt_basis(N, sizeP, p, sizeQ, q, t, s, count);
     for (u64 c = 0; c < count; ++c)
         for (u32 i = 0; i < sizeQ; ++i) {
             u64* si = s + (c * sizeQ + i) * N;
+            if (ptm > 0)
+                for (u32 k = 0; k < N; ++k) si[k] = mulmod(si[k], ptm % q[i], q[i]);
             orc_ntt(q[i], orc_root_of_unity(2 * (u64)N, q[i]), N, si, 1, 0, 1);
             u64 pinv = 1;
             for (u32 j = 0; j < sizeP; ++j) pinv = mulmod(pinv, p[j] % q[i], q[i]);
@@ -953,6 +962,9 @@ int orc_approx_mod_down(u32 N, u32 sizeQ, const u64* q, u32 sizeP, const u64* p,
         }
     free(t); free(s);
     return 0;
+}
+int orc_approx_mod_down(u32 N, u32 sizeQ, const u64* q, u32 sizeP, const u64* p, const u64* x, u64* out, u64 count) {
+    return orc_approx_mod_down_t(N, sizeQ, q, sizeP, p, x, out, count, 0);
 }
 
 double orc_time_bingate(OrcCtx* c, int gate, const u64* a1, const u64* b1, const u64* a2, const u64* b2, u64* oa,

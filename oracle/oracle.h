@@ -83,6 +83,8 @@ int orc_approx_mod_up(uint32_t N, uint32_t sizeQ, const uint64_t* q, uint32_t si
                       uint64_t* out, uint64_t count);
 int orc_approx_mod_down(uint32_t N, uint32_t sizeQ, const uint64_t* q, uint32_t sizeP, const uint64_t* p, const uint64_t* x,
                         uint64_t* out, uint64_t count);
+int orc_approx_mod_down_t(uint32_t N, uint32_t sizeQ, const uint64_t* q, uint32_t sizeP, const uint64_t* p, const uint64_t* x,
+                          uint64_t* out, uint64_t count, uint64_t ptm);   /* ptm > 0: the BGV branch */
 double orc_time_bingate(OrcCtx*, int gate, const uint64_t* a1, const uint64_t* b1, const uint64_t* a2,
                         const uint64_t* b2, uint64_t* oa, uint64_t* ob, uint64_t count, int threads);
 int orc_max_threads(void);

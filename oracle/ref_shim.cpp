@@ -598,8 +598,19 @@ RnsTables rns_tables(const std::vector<NativeInteger>& from, const std::vector<N
 // x [count][limbs_in][N] -> out [count][limbs_out][N].  what 0: ApproxSwitchCRTBasis Q -> P on COEFFICIENT data (sizeQ in,
 // sizeP out); 1: ApproxModUp, EVALUATION (sizeQ in, sizeQ + sizeP out); 2: ApproxModDown with t = 0, EVALUATION (sizeQ + sizeP
 // in, sizeQ out)
+static int ref_rns_op_t(uint32_t N, uint32_t sizeQ, const uint64_t* q, uint32_t sizeP, const uint64_t* p, const uint64_t* x, uint64_t* out,
+                        uint64_t count, int what, uint64_t ptm);
 int ref_rns_op(uint32_t N, uint32_t sizeQ, const uint64_t* q, uint32_t sizeP, const uint64_t* p, const uint64_t* x, uint64_t* out,
                uint64_t count, int what) {
+    return ref_rns_op_t(N, sizeQ, q, sizeP, p, x, out, count, what, 0);
+}
+// ApproxModDown with the BGV tables of bgvrns-cryptoparameters.cpp:78-95 (tInvModp = t^-1 mod p_j, tModqPrecon) and t = ptm
+int ref_rns_moddown_t(uint32_t N, uint32_t sizeQ, const uint64_t* q, uint32_t sizeP, const uint64_t* p, const uint64_t* x, uint64_t* out,
+                      uint64_t count, uint64_t ptm) {
+    return ref_rns_op_t(N, sizeQ, q, sizeP, p, x, out, count, 2, ptm);
+}
+static int ref_rns_op_t(uint32_t N, uint32_t sizeQ, const uint64_t* q, uint32_t sizeP, const uint64_t* p, const uint64_t* x, uint64_t* out,
+                        uint64_t count, int what, uint64_t ptm) {
     try {
         std::vector<NativeInteger> mq, mp, rq, rp, mqp, rqp;
         for (uint32_t i = 0; i < sizeQ; ++i) { mq.emplace_back(q[i]); rq.push_back(RootOfUnity<NativeInteger>(2 * N, mq.back())); }
@@ -628,8 +639,16 @@ int ref_rns_op(uint32_t N, uint32_t sizeQ, const uint64_t* q, uint32_t sizeP, co
             DCRTPoly res;
             if (what == 0) res = in.ApproxSwitchCRTBasis(paramsQ, paramsP, up.hatInv, up.hatInvPrecon, up.hatMod, up.mu);
             else if (what == 1) { in.ApproxModUp(paramsQ, paramsP, paramsQP, up.hatInv, up.hatInvPrecon, up.hatMod, up.mu); res = in; }
-            else res = in.ApproxModDown(paramsQ, paramsP, pInv, pInvPrecon, down.hatInv, down.hatInvPrecon, down.hatMod, down.mu, {}, {},
-                                        NativeInteger(0), {});
+            else if (ptm == 0) res = in.ApproxModDown(paramsQ, paramsP, pInv, pInvPrecon, down.hatInv, down.hatInvPrecon, down.hatMod, down.mu, {}, {},
+                                                      NativeInteger(0), {});
+            else {
+                const NativeInteger t(ptm);
+                std::vector<NativeInteger> tInvModp, tInvModpPrecon, tModqPrecon;
+                for (auto& pj : mp) { tInvModp.push_back(t.ModInverse(pj)); tInvModpPrecon.push_back(tInvModp.back().PrepModMulConst(pj)); }
+                for (auto& qi : mq) tModqPrecon.push_back(t.Mod(qi).PrepModMulConst(qi));
+                res = in.ApproxModDown(paramsQ, paramsP, pInv, pInvPrecon, down.hatInv, down.hatInvPrecon, down.hatMod, down.mu, tInvModp,
+                                       tInvModpPrecon, t, tModqPrecon);
+            }
             if (res.GetNumOfElements() != lout) return -2;
             for (uint32_t l = 0; l < lout; ++l) {
                 const NativePoly& limb = res.GetAllElements()[l];

@@ -771,4 +771,8 @@ def test_rns_basis_conversion_vs_oracle(N, sizeQ, sizeP, bits, cnt):
     ref = np.zeros((cnt, sizeQ, N), np.uint64)
     O.orc_approx_mod_down(N, sizeQ, P(q), sizeP, P(p), P(xqp), P(ref), cnt)
     assert (pl.ApproxModDown(xqp) == ref).all()
+    for t in (65537, 2, (1 << 40) + 15):   # the BGV branch (plaintext modulus t), incl. a t above 32 bits
+        O.orc_approx_mod_down_t(N, sizeQ, P(q), sizeP, P(p), P(xqp), P(ref), cnt, t)
+        assert (pl.ApproxModDown(xqp, t) == ref).all(), t
+    assert (pl.ApproxModDown(xqp, 0) == pl.ApproxModDown(xqp)).all()
     pl.close()

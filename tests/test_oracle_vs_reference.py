@@ -194,3 +194,9 @@ def test_rns_basis_conversion_pins_the_oracle(N, sizeQ, sizeP, bits):
         assert R.ref_rns_op(N, sizeQ, P(q), sizeP, P(p), P(inp), P(a), cnt, what) == 0
         assert fn(N, sizeQ, P(q), sizeP, P(p), P(inp), P(b), cnt) == 0
         assert (a == b).all(), what
+    # the BGV branch of ApproxModDown (plaintext modulus t > 0; tables of bgvrns-cryptoparameters.cpp:78-95)
+    for t in (65537, 2, (1 << 40) + 15):
+        a = np.zeros((cnt, sizeQ, N), np.uint64); b = a.copy()
+        assert R.ref_rns_moddown_t(N, sizeQ, P(q), sizeP, P(p), P(xqp), P(a), cnt, t) == 0
+        assert O.orc_approx_mod_down_t(N, sizeQ, P(q), sizeP, P(p), P(xqp), P(b), cnt, t) == 0
+        assert (a == b).all(), t
