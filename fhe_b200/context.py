@@ -440,6 +440,17 @@ class RNSPlan:
         _l.check(self.L.luxb200_approx_mod_switch(self.h, _l.ptr(x), _l.ptr(out), x.shape[0], 0))
         return out
 
+    def KeySwitchInner(self, digits, evk_b, evk_a, sizeQl=None):
+        """KeySwitchHYBRID::EvalFastKeySwitchCoreExt (keyswitch-hybrid.cpp:438-481): digits [count][nd][sizeQl + sizeP][N], the key's
+        b and a vectors [nd][sizeQ + sizeP][N] -> [count][2][sizeQl + sizeP][N]."""
+        digits = np.ascontiguousarray(digits, np.uint64)
+        evk_b = np.ascontiguousarray(evk_b, np.uint64); evk_a = np.ascontiguousarray(evk_a, np.uint64)
+        cnt, nd, L = digits.shape[0], digits.shape[1], digits.shape[2]
+        sizeQl = L - len(self.p) if sizeQl is None else sizeQl
+        out = np.empty((cnt, 2, L, self.N), np.uint64)
+        _l.check(self.L.luxb200_rns_keyswitch_inner(self.h, _l.ptr(digits), _l.ptr(evk_b), _l.ptr(evk_a), _l.ptr(out), cnt, nd, sizeQl))
+        return out
+
     def ApproxModDown(self, x, t=0):
         """t = 0: CKKS; t > 0: the BGV branch with plaintext modulus t (dcrtpoly-impl.h:1003-1005, :1021-1023)."""
         x = np.ascontiguousarray(x, np.uint64)

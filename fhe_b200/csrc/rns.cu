@@ -76,6 +76,47 @@ __global__ void rns_moddown_tail_kernel(const u64* __restrict__ x, u32 x_stride,
     out[gid] = r >= qi ? r - qi : r;
 }
 
+// 128-bit sum -> canonical residue mod m (m < 2^62): the high word folded with a Shoup multiplication by r = 2^64 mod m, the low
+// word with a Barrett step (mu = floor(2^64 / m)), both in [0, 2m)
+__device__ __forceinline__ u64 rns_reduce128(u128 s, u64 m, u64 mu, u64 r, u64 rs) {
+    const u64 lo = (u64)s, hi = (u64)(s >> 64);
+    const u64 t = hi * r - __umul64hi(hi, rs) * m;
+    const u64 l = lo - __umul64hi(lo, mu) * m;
+    u64 v = t + l;
+    v = v >= 2 * m ? v - 2 * m : v;
+    return v >= m ? v - m : v;
+}
+
+// KeySwitchHYBRID::EvalFastKeySwitchCoreExt (keyswitch-hybrid.cpp:438-481): out_c[i][k] = sum_j digits_j[i][k] * evk_c[j][idx(i)][k]
+// mod m_i over the basis Ql u P; one thread per (ciphertext, limb, coefficient), exact 128-bit sums reduced once per four terms
+// (any exact evaluation gives the reference's canonical residues).  HBM-bound: 24 bytes read per digit, 16 written.
+struct RnsInner {
+    const u64 *qm, *qmu, *qr, *qrs;   // Q moduli and their reduction constants
+    const u64 *pm, *pmu, *pr, *prs;   // P moduli
+    u32 sizeQ, sizeP, sizeQl, nd, N, pad;
+};
+__global__ void __launch_bounds__(256) rns_inner_kernel(const RnsInner D, const u64* __restrict__ digits, const u64* __restrict__ kb,
+                                                        const u64* __restrict__ ka, u64* __restrict__ out, u64 count) {
+    const u32 L = D.sizeQl + D.sizeP, LK = D.sizeQ + D.sizeP;
+    const u64 gid = (u64)blockIdx.x * blockDim.x + threadIdx.x;
+    if (gid >= count * L * D.N) return;
+    const u32 k = (u32)(gid % D.N);
+    const u32 i = (u32)((gid / D.N) % L);
+    const u64 c = gid / ((u64)D.N * L);
+    const bool isq = i < D.sizeQl;
+    const u32 li = isq ? i : i - D.sizeQl, idx = isq ? i : D.sizeQ + li;
+    const u64 m = isq ? D.qm[li] : D.pm[li], mu = isq ? D.qmu[li] : D.pmu[li], r = isq ? D.qr[li] : D.pr[li], rs = isq ? D.qrs[li] : D.prs[li];
+    u128 s0 = 0, s1 = 0;
+    for (u32 j = 0; j < D.nd; ++j) {
+        const u64 d = digits[((c * D.nd + j) * L + i) * D.N + k];
+        s0 += (u128)d * kb[((u64)j * LK + idx) * D.N + k];
+        s1 += (u128)d * ka[((u64)j * LK + idx) * D.N + k];
+        if ((j & 3) == 3) { s0 = rns_reduce128(s0, m, mu, r, rs); s1 = rns_reduce128(s1, m, mu, r, rs); }   // 4 m^2 + m < 2^128
+    }
+    out[((c * 2 + 0) * L + i) * D.N + k] = rns_reduce128(s0, m, mu, r, rs);
+    out[((c * 2 + 1) * L + i) * D.N + k] = rns_reduce128(s1, m, mu, r, rs);
+}
+
 // data[c][l][k] <- data[c][l][k] * w_l mod m_l (canonical in, canonical out): the BGV factors of ApproxModDown, t^-1 mod p_j on the
 // P part before the basis switch and t mod q_i on the switched part (dcrtpoly-impl.h:1003-1005, :1021-1023)
 __global__ void rns_scale_limbs_kernel(u64* __restrict__ data, const u64* __restrict__ mod, const u64* __restrict__ w,
@@ -381,6 +422,49 @@ int luxb200_approx_switch_crt_basis_static(luxb200_rns_plan* pl, const uint64_t*
     LB_TRY(launch_switch(pl, D, sin, D.sizeQ, 0, sout, D.sizeP, 0, count));
     LB_CUDA(cudaMemcpyAsync(out, sout, count * out_el * 8, cudaMemcpyDeviceToHost, pl->stream));
     LB_CUDA(cudaStreamSynchronize(pl->stream));
+    return 0;
+}
+
+// EvalFastKeySwitchCoreExt: digits [count][nd][sizeQl + sizeP][N], evk_b / evk_a [nd][sizeQ + sizeP][N] (the key on the full
+// basis), out [count][2][sizeQl + sizeP][N]; everything EVALUATION format on the plan's device
+int luxb200_rns_keyswitch_inner_dev(luxb200_rns_plan* pl, const void* digits_dev, const void* evk_b_dev, const void* evk_a_dev,
+                                    void* out_dev, uint64_t count, uint32_t nd, uint32_t sizeQl) {
+    if (!pl || !digits_dev || !evk_b_dev || !evk_a_dev || !out_dev) return lb_fail(LUXB200_ERR_INVALID_ARG, "null argument");
+    if (nd == 0 || sizeQl == 0 || sizeQl > pl->sizeQ) return lb_fail(LUXB200_ERR_INVALID_ARG, "need 1 <= sizeQl <= sizeQ and at least one digit");
+    if (count == 0) return 0;
+    LB_TRY(lb_set_device(pl->device));
+    RnsInner D;
+    D.qm = pl->d_down.p; D.qmu = pl->d_down.pmu; D.qr = pl->d_down.pr; D.qrs = pl->d_down.prs;   // the P -> Q tables target Q
+    D.pm = pl->d_up.p;   D.pmu = pl->d_up.pmu;   D.pr = pl->d_up.pr;   D.prs = pl->d_up.prs;
+    D.sizeQ = pl->sizeQ; D.sizeP = pl->sizeP; D.sizeQl = sizeQl; D.nd = nd; D.N = pl->N; D.pad = 0;
+    const u64 total = count * (sizeQl + pl->sizeP) * pl->N;
+    rns_inner_kernel<<<nblk(total, 256), 256, 0, pl->stream>>>(D, reinterpret_cast<const u64*>(digits_dev), reinterpret_cast<const u64*>(evk_b_dev),
+                                                             reinterpret_cast<const u64*>(evk_a_dev), reinterpret_cast<u64*>(out_dev), count);
+    LB_CUDA(cudaGetLastError());
+    LB_CUDA(cudaStreamSynchronize(pl->stream));
+    return 0;
+}
+// host buffers (the key is uploaded with every call: callers that keep it resident use the _dev form)
+int luxb200_rns_keyswitch_inner(luxb200_rns_plan* pl, const uint64_t* digits, const uint64_t* evk_b, const uint64_t* evk_a, uint64_t* out,
+                                uint64_t count, uint32_t nd, uint32_t sizeQl) {
+    if (!pl || !digits || !evk_b || !evk_a || !out) return lb_fail(LUXB200_ERR_INVALID_ARG, "null argument");
+    if (nd == 0 || sizeQl == 0 || sizeQl > pl->sizeQ) return lb_fail(LUXB200_ERR_INVALID_ARG, "need 1 <= sizeQl <= sizeQ and at least one digit");
+    if (count == 0) return 0;
+    LB_TRY(lb_set_device(pl->device));
+    const uint64_t L = sizeQl + pl->sizeP, LK = pl->sizeQ + pl->sizeP, N = pl->N;
+    const uint64_t key_el = (uint64_t)nd * LK * N, in_el = (uint64_t)nd * L * N, out_el = 2 * L * N;
+    LB_TRY(pl->tmpQ.ensure(2 * key_el * 8));
+    LB_CUDA(cudaMemcpyAsync(pl->tmpQ.p, evk_b, key_el * 8, cudaMemcpyHostToDevice, pl->stream));
+    LB_CUDA(cudaMemcpyAsync(pl->tmpQ.as<u64>() + key_el, evk_a, key_el * 8, cudaMemcpyHostToDevice, pl->stream));
+    const uint64_t chunk = std::max<uint64_t>(1, (256ull << 20) / ((in_el + out_el) * 8));
+    for (uint64_t off = 0; off < count; off += chunk) {
+        const uint64_t m = std::min(chunk, count - off);
+        LB_TRY(pl->stage_in.ensure(m * in_el * 8)); LB_TRY(pl->stage_out.ensure(m * out_el * 8));
+        LB_CUDA(cudaMemcpyAsync(pl->stage_in.p, digits + off * in_el, m * in_el * 8, cudaMemcpyHostToDevice, pl->stream));
+        LB_TRY(luxb200_rns_keyswitch_inner_dev(pl, pl->stage_in.p, pl->tmpQ.p, pl->tmpQ.as<u64>() + key_el, pl->stage_out.p, m, nd, sizeQl));
+        LB_CUDA(cudaMemcpyAsync(out + off * out_el, pl->stage_out.p, m * out_el * 8, cudaMemcpyDeviceToHost, pl->stream));
+        LB_CUDA(cudaStreamSynchronize(pl->stream));
+    }
     return 0;
 }
 

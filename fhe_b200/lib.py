@@ -82,6 +82,8 @@ SIGNATURES = {
     "luxb200_approx_mod_up_dev": (INT, [VP, VP, VP, U64]),
     "luxb200_approx_mod_down_dev": (INT, [VP, VP, VP, U64]),
     "luxb200_approx_mod_switch_bgv": (INT, [VP, VP, VP, U64, INT, U64]),
+    "luxb200_rns_keyswitch_inner": (INT, [VP, VP, VP, VP, VP, U64, U32, U32]),
+    "luxb200_rns_keyswitch_inner_dev": (INT, [VP, VP, VP, VP, VP, U64, U32, U32]),
     "luxb200_approx_mod_down_bgv_dev": (INT, [VP, VP, VP, U64, U64]),
     "luxb200_evalbingate_batch_dev": (INT, [VP, INT, VP, VP, VP, VP, VP, VP, U64]),
     "luxb200_circuit_batch": (INT, [VP, U32, VP, U32, VP, U32, VP, VP, VP, VP, U64]),

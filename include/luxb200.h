@@ -209,6 +209,15 @@ int luxb200_approx_mod_down_dev(luxb200_rns_plan* plan, const void* x_dev, void*
  * (t is ignored for what = 0). */
 int luxb200_approx_mod_switch_bgv(luxb200_rns_plan* plan, const uint64_t* x, uint64_t* out, uint64_t count, int what, uint64_t t);
 int luxb200_approx_mod_down_bgv_dev(luxb200_rns_plan* plan, const void* x_dev, void* out_dev, uint64_t count, uint64_t t);
+/* KeySwitchHYBRID::EvalFastKeySwitchCoreExt (src/pke/lib/keyswitch/keyswitch-hybrid.cpp:438-481), the inner product of hybrid key
+ * switching between ApproxModUp and ApproxModDown: over the basis Ql u P (the first sizeQl moduli of the plan's Q, then P),
+ * out_c[i] = sum_j digits_j[i] * evk_c[j][idx(i)] mod m_i, c = 0 the key's b vector, c = 1 its a vector, idx(i) = i for a Q limb and
+ * sizeQ + (i - sizeQl) for a P limb.  EVALUATION format; digits [count][nd][sizeQl + sizeP][N], evk_b / evk_a
+ * [nd][sizeQ + sizeP][N], out [count][2][sizeQl + sizeP][N].  Host buffers, or device pointers for the _dev form. */
+int luxb200_rns_keyswitch_inner(luxb200_rns_plan* plan, const uint64_t* digits, const uint64_t* evk_b, const uint64_t* evk_a,
+                                uint64_t* out, uint64_t count, uint32_t nd, uint32_t sizeQl);
+int luxb200_rns_keyswitch_inner_dev(luxb200_rns_plan* plan, const void* digits_dev, const void* evk_b_dev, const void* evk_a_dev,
+                                    void* out_dev, uint64_t count, uint32_t nd, uint32_t sizeQl);
 /* Allocation-free variant of luxb200_approx_switch_crt_basis.  It has no counterpart in the reference and was added
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
  * harnesses that forbid it).  Same arguments, same result; the device staging of the basis-switch kernel is a static device

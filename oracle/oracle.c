@@ -963,6 +963,30 @@ int orc_approx_mod_down_t(u32 N, u32 sizeQ, const u64* q, u32 sizeP, const u64* 
     free(t); free(s);
     return 0;
 }
+/* KeySwitchHYBRID::EvalFastKeySwitchCoreExt (src/pke/lib/keyswitch/keyswitch-hybrid.cpp:438-481): over the basis Ql u P (the
+ * first sizeQl moduli of Q, then P), out_c[i] = sum_j digits_j[i] * evk_c[j][idx(i)] mod m_i with c = 0 the key's b vector and
+ * c = 1 its a vector, idx(i) = i for a Q limb and sizeQ + (i - sizeQl) for a P limb (the key lives on the full Q u P).
+ * digits [count][nd][sizeQl + sizeP][N], evk_b / evk_a [nd][sizeQ + sizeP][N], out [count][2][sizeQl + sizeP][N] */
+int orc_keyswitch_inner(u32 N, u32 sizeQ, const u64* q, u32 sizeP, const u64* p, u32 sizeQl, u32 nd, const u64* digits,
+                        const u64* evk_b, const u64* evk_a, u64* out, u64 count) {
+    const u32 L = sizeQl + sizeP, LK = sizeQ + sizeP;
+    for (u64 c = 0; c < count; ++c)
+        for (u32 i = 0; i < L; ++i) {
+            const u64 m = i < sizeQl ? q[i] : p[i - sizeQl];
+            const u32 idx = i < sizeQl ? i : sizeQ + (i - sizeQl);
+            for (u32 k = 0; k < N; ++k) {
+                u64 s0 = 0, s1 = 0;
+                for (u32 j = 0; j < nd; ++j) {
+                    const u64 d = digits[((c * nd + j) * L + i) * N + k];
+                    s0 = addmod(s0, mulmod(d, evk_b[((u64)j * LK + idx) * N + k], m), m);
+                    s1 = addmod(s1, mulmod(d, evk_a[((u64)j * LK + idx) * N + k], m), m);
+                }
+                out[((c * 2 + 0) * L + i) * N + k] = s0;
+                out[((c * 2 + 1) * L + i) * N + k] = s1;
+            }
+        }
+    return 0;
+}
 int orc_approx_mod_down(u32 N, u32 sizeQ, const u64* q, u32 sizeP, const u64* p, const u64* x, u64* out, u64 count) {
     return orc_approx_mod_down_t(N, sizeQ, q, sizeP, p, x, out, count, 0);
 }

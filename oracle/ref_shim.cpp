@@ -662,6 +662,58 @@ static int ref_rns_op_t(uint32_t N, uint32_t sizeQ, const uint64_t* q, uint32_t 
     }
 }
 
+// The loop body of KeySwitchHYBRID::EvalFastKeySwitchCoreExt (keyswitch-hybrid.cpp:457-477) on the reference's own DCRTPoly /
+// NativePoly objects: cTilda_c[i] += cj[i] * (b|a)_j[idx(i)].  (The function itself needs an EvalKey with crypto parameters; its
+// arithmetic is exactly these element operations.)  Layouts as orc_keyswitch_inner.
+int ref_keyswitch_inner(uint32_t N, uint32_t sizeQ, const uint64_t* q, uint32_t sizeP, const uint64_t* p, uint32_t sizeQl, uint32_t nd,
+                        const uint64_t* digits, const uint64_t* evk_b, const uint64_t* evk_a, uint64_t* out, uint64_t count) {
+    try {
+        std::vector<NativeInteger> mqlp, rqlp, mqp, rqp;
+        for (uint32_t i = 0; i < sizeQl; ++i) { mqlp.emplace_back(q[i]); rqlp.push_back(RootOfUnity<NativeInteger>(2 * N, mqlp.back())); }
+        for (uint32_t j = 0; j < sizeP; ++j) { mqlp.emplace_back(p[j]); rqlp.push_back(RootOfUnity<NativeInteger>(2 * N, mqlp.back())); }
+        for (uint32_t i = 0; i < sizeQ; ++i) { mqp.emplace_back(q[i]); rqp.push_back(RootOfUnity<NativeInteger>(2 * N, mqp.back())); }
+        for (uint32_t j = 0; j < sizeP; ++j) { mqp.emplace_back(p[j]); rqp.push_back(RootOfUnity<NativeInteger>(2 * N, mqp.back())); }
+        auto paramsQlP = std::make_shared<ILDCRTParams<BigInteger>>(2 * N, mqlp, rqlp);
+        auto paramsQP  = std::make_shared<ILDCRTParams<BigInteger>>(2 * N, mqp, rqp);
+        const uint32_t L = sizeQl + sizeP, LK = sizeQ + sizeP;
+        auto fill = [&](DCRTPoly& d, const uint64_t* src, uint32_t limbs) {
+            for (uint32_t l = 0; l < limbs; ++l) {
+                NativePoly& limb = d.GetAllElements()[l];
+                for (uint32_t k = 0; k < N; ++k) limb[k] = NativeInteger(src[(size_t)l * N + k]);
+            }
+        };
+        std::vector<DCRTPoly> bv, av;
+        for (uint32_t j = 0; j < nd; ++j) {
+            bv.emplace_back(paramsQP, Format::EVALUATION, true); fill(bv.back(), evk_b + (size_t)j * LK * N, LK);
+            av.emplace_back(paramsQP, Format::EVALUATION, true); fill(av.back(), evk_a + (size_t)j * LK * N, LK);
+        }
+        for (uint64_t c = 0; c < count; ++c) {
+            DCRTPoly cTilda0(paramsQlP, Format::EVALUATION, true), cTilda1(paramsQlP, Format::EVALUATION, true);
+            for (uint32_t j = 0; j < nd; ++j) {
+                DCRTPoly cj(paramsQlP, Format::EVALUATION, true);
+                fill(cj, digits + ((size_t)c * nd + j) * L * N, L);
+                for (uint32_t i = 0; i < sizeQl; ++i) {
+                    cTilda0.SetElementAtIndex(i, cTilda0.GetElementAtIndex(i) + cj.GetElementAtIndex(i) * bv[j].GetElementAtIndex(i));
+                    cTilda1.SetElementAtIndex(i, cTilda1.GetElementAtIndex(i) + cj.GetElementAtIndex(i) * av[j].GetElementAtIndex(i));
+                }
+                for (uint32_t i = sizeQl, idx = sizeQ; i < L; ++i, ++idx) {
+                    cTilda0.SetElementAtIndex(i, cTilda0.GetElementAtIndex(i) + cj.GetElementAtIndex(i) * bv[j].GetElementAtIndex(idx));
+                    cTilda1.SetElementAtIndex(i, cTilda1.GetElementAtIndex(i) + cj.GetElementAtIndex(i) * av[j].GetElementAtIndex(idx));
+                }
+            }
+            for (uint32_t l = 0; l < L; ++l)
+                for (uint32_t k = 0; k < N; ++k) {
+                    out[(((size_t)c * 2 + 0) * L + l) * N + k] = cTilda0.GetAllElements()[l][k].ConvertToInt<uint64_t>();
+                    out[(((size_t)c * 2 + 1) * L + l) * N + k] = cTilda1.GetAllElements()[l][k].ConvertToInt<uint64_t>();
+                }
+        }
+        return 0;
+    }
+    catch (...) {
+        return -1;
+    }
+}
+
 // ---- CPU baseline timers (bench.py --impl reference / cpu_baseline) --------------------------------
 // `count` EvalBinGate(gate) on count ciphertext pairs, outer OMP loop over independent gates — the shape
 // of EvalBinGateBatch (src/binfhe/lib/batch/batch.cpp:197-200). Returns seconds.

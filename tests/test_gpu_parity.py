@@ -775,4 +775,14 @@ def test_rns_basis_conversion_vs_oracle(N, sizeQ, sizeP, bits, cnt):
         O.orc_approx_mod_down_t(N, sizeQ, P(q), sizeP, P(p), P(xqp), P(ref), cnt, t)
         assert (pl.ApproxModDown(xqp, t) == ref).all(), t
     assert (pl.ApproxModDown(xqp, 0) == pl.ApproxModDown(xqp)).all()
+    # the inner product of hybrid key switching (EvalFastKeySwitchCoreExt) on the full and on a truncated basis, 3 and 6 digits
+    for nd, sizeQl in ((3, sizeQ), (6, max(1, sizeQ - 1))):
+        mods_l = list(q[:sizeQl]) + list(p)
+        dg = np.stack([np.stack([np.stack([rng.integers(0, int(m), size=N, dtype=np.uint64) for m in mods_l]) for _ in range(nd)]) for _ in range(cnt)])
+        kb = np.stack([np.stack([rng.integers(0, int(m), size=N, dtype=np.uint64) for m in chain]) for _ in range(nd)])
+        ka = np.stack([np.stack([rng.integers(0, int(m), size=N, dtype=np.uint64) for m in chain]) for _ in range(nd)])
+        dg[0, :, :, 0] = np.array(mods_l, np.uint64) - np.uint64(1); kb[:, :, 0] = chain - np.uint64(1)   # (m - 1)^2 in every term
+        ref = np.zeros((cnt, 2, sizeQl + sizeP, N), np.uint64)
+        O.orc_keyswitch_inner(N, sizeQ, P(q), sizeP, P(p), sizeQl, nd, P(dg), P(kb), P(ka), P(ref), cnt)
+        assert (pl.KeySwitchInner(dg, kb, ka, sizeQl) == ref).all(), (nd, sizeQl)
     pl.close()

@@ -194,6 +194,19 @@ def test_rns_basis_conversion_pins_the_oracle(N, sizeQ, sizeP, bits):
         assert R.ref_rns_op(N, sizeQ, P(q), sizeP, P(p), P(inp), P(a), cnt, what) == 0
         assert fn(N, sizeQ, P(q), sizeP, P(p), P(inp), P(b), cnt) == 0
         assert (a == b).all(), what
+    # the inner product of EvalFastKeySwitchCoreExt (keyswitch-hybrid.cpp:438-481) on a truncated basis Ql u P
+    nd, sizeQl = 3, max(1, sizeQ - 1)
+    L, LK = sizeQl + sizeP, sizeQ + sizeP
+    mods_l = list(q[:sizeQl]) + list(p)
+    dg = np.stack([np.stack([np.stack([rng.integers(0, int(m), size=N, dtype=np.uint64) for m in mods_l]) for _ in range(nd)]) for _ in range(cnt)])
+    dg[0, 0, 0, :] = q[0] - np.uint64(1)
+    kb = np.stack([np.stack([rng.integers(0, int(m), size=N, dtype=np.uint64) for m in chain]) for _ in range(nd)])
+    ka = np.stack([np.stack([rng.integers(0, int(m), size=N, dtype=np.uint64) for m in chain]) for _ in range(nd)])
+    kb[0, 0, :] = q[0] - np.uint64(1)
+    a = np.zeros((cnt, 2, L, N), np.uint64); b = a.copy()
+    assert R.ref_keyswitch_inner(N, sizeQ, P(q), sizeP, P(p), sizeQl, nd, P(dg), P(kb), P(ka), P(a), cnt) == 0
+    assert O.orc_keyswitch_inner(N, sizeQ, P(q), sizeP, P(p), sizeQl, nd, P(dg), P(kb), P(ka), P(b), cnt) == 0
+    assert (a == b).all()
     # the BGV branch of ApproxModDown (plaintext modulus t > 0; tables of bgvrns-cryptoparameters.cpp:78-95)
     for t in (65537, 2, (1 << 40) + 15):
         a = np.zeros((cnt, sizeQ, N), np.uint64); b = a.copy()
