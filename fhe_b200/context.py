@@ -462,3 +462,32 @@ class RNSPlan:
         if self.h:
             self.L.luxb200_rns_plan_destroy(self.h)
             self.h = None
+
+
+class HybridKeySwitchPlan:
+    """KeySwitchHYBRID::EvalKeySwitchPrecomputeCore + EvalFastKeySwitchCore (src/pke/lib/keyswitch/keyswitch-hybrid.cpp:328-436) for
+    one polynomial over Ql = q[:sizeQl]: c [count][sizeQl][N] EVALUATION, the key's b / a vectors [num_digits][len(q) + len(p)][N] ->
+    [count][2][sizeQl][N]; t = 0 CKKS, t > 0 BGV."""
+
+    def __init__(self, N, q, p, alpha, sizeQl=None, device=0):
+        self.L = _l.load()
+        self.q = np.ascontiguousarray(q, np.uint64)
+        self.p = np.ascontiguousarray(p, np.uint64)
+        self.N, self.sizeQl = N, len(self.q) if sizeQl is None else sizeQl
+        h = _l.VP()
+        _l.check(self.L.luxb200_hks_plan_create(N, len(self.q), _l.ptr(self.q), len(self.p), _l.ptr(self.p), alpha, self.sizeQl, device,
+                                                C.byref(h)))
+        self.h = h
+        self.num_digits = int(self.L.luxb200_hks_num_digits(self.h))
+
+    def KeySwitch(self, c, evk_b, evk_a, t=0):
+        c = np.ascontiguousarray(c, np.uint64)
+        evk_b = np.ascontiguousarray(evk_b, np.uint64); evk_a = np.ascontiguousarray(evk_a, np.uint64)
+        out = np.empty((c.shape[0], 2, self.sizeQl, self.N), np.uint64)
+        _l.check(self.L.luxb200_hks_keyswitch(self.h, _l.ptr(c), _l.ptr(evk_b), _l.ptr(evk_a), _l.ptr(out), c.shape[0], int(t)))
+        return out
+
+    def close(self):
+        if self.h:
+            self.L.luxb200_hks_plan_destroy(self.h)
+            self.h = None

@@ -185,6 +185,14 @@ struct luxb200_rns_plan {
     cudaStream_t stream = nullptr;
 };
 
+struct luxb200_hks_plan {
+    uint32_t N = 0, sizeQ = 0, sizeP = 0, alpha = 0, sizeQl = 0, nd = 0;
+    int device = 0;
+    std::vector<luxb200_rns_plan*> parts;              // per digit: source = the part's limbs, target = every other limb of Ql u P
+    luxb200_rns_plan *full = nullptr, *down = nullptr; // (Q, P): inner-product constants; (Ql, P): ApproxModDown
+    DevBuf cin, part_in, part_out, digits, tilda, key, outb;
+};
+
 namespace {
 
 int upload_tables(const Tables& T, DevBuf& buf, RnsDev& D, u32 N) {
@@ -464,6 +472,88 @@ int luxb200_rns_keyswitch_inner(luxb200_rns_plan* pl, const uint64_t* digits, co
         LB_TRY(luxb200_rns_keyswitch_inner_dev(pl, pl->stage_in.p, pl->tmpQ.p, pl->tmpQ.as<u64>() + key_el, pl->stage_out.p, m, nd, sizeQl));
         LB_CUDA(cudaMemcpyAsync(out + off * out_el, pl->stage_out.p, m * out_el * 8, cudaMemcpyDeviceToHost, pl->stream));
         LB_CUDA(cudaStreamSynchronize(pl->stream));
+    }
+    return 0;
+}
+
+// ---- hybrid key switching of one polynomial: KeySwitchHYBRID::EvalKeySwitchPrecomputeCore (keyswitch-hybrid.cpp:328-412) and
+// EvalFastKeySwitchCore (:414-436) as one call over the primitives above.  A digit = `alpha` consecutive limbs of Ql raised to
+// Ql u P by ApproxSwitchCRTBasis from its own limbs to all the others (one rns plan per part: source = the part, target = the
+// complement), the inner product with the key, ApproxModDown of both results.
+int luxb200_hks_plan_create(uint32_t N, uint32_t sizeQ, const uint64_t* q, uint32_t sizeP, const uint64_t* p, uint32_t alpha,
+                            uint32_t sizeQl, int device, luxb200_hks_plan** out) {
+    if (!q || !p || !out) return lb_fail(LUXB200_ERR_INVALID_ARG, "null argument");
+    *out = nullptr;
+    if (alpha == 0 || sizeQl == 0 || sizeQl > sizeQ || sizeP == 0) return lb_fail(LUXB200_ERR_INVALID_ARG, "need alpha >= 1, 1 <= sizeQl <= sizeQ, sizeP >= 1");
+    auto* h = new luxb200_hks_plan();
+    h->N = N; h->sizeQ = sizeQ; h->sizeP = sizeP; h->alpha = alpha; h->sizeQl = sizeQl; h->device = device;
+    h->nd = std::min((sizeQl + alpha - 1) / alpha, (sizeQ + alpha - 1) / alpha);
+    const uint32_t L = sizeQl + sizeP;
+    int rc = luxb200_rns_plan_create(N, sizeQ, q, sizeP, p, device, &h->full);
+    if (!rc) rc = luxb200_rns_plan_create(N, sizeQl, q, sizeP, p, device, &h->down);
+    for (uint32_t part = 0; part < h->nd && !rc; ++part) {
+        const uint32_t start = alpha * part, sp = (part == h->nd - 1) ? sizeQl - start : alpha, end = start + sp;
+        std::vector<uint64_t> src(q + start, q + end), dst;
+        for (uint32_t i = 0; i < L; ++i)
+            if (i < start || i >= end) dst.push_back(i < sizeQl ? q[i] : p[i - sizeQl]);
+        luxb200_rns_plan* pp = nullptr;
+        rc = luxb200_rns_plan_create(N, sp, src.data(), (uint32_t)dst.size(), dst.data(), device, &pp);
+        if (!rc && !pp->nttQ) rc = lb_fail(LUXB200_ERR_UNSUPPORTED, "N or the moduli do not admit an NTT");
+        h->parts.push_back(pp);
+    }
+    if (!rc && (!h->full->nttQ || !h->down->nttQ)) rc = lb_fail(LUXB200_ERR_UNSUPPORTED, "N or the moduli do not admit an NTT");
+    if (rc) { luxb200_hks_plan_destroy(h); return rc; }
+    *out = h;
+    return 0;
+}
+void luxb200_hks_plan_destroy(luxb200_hks_plan* h) {
+    if (!h) return;
+    for (auto* pp : h->parts) luxb200_rns_plan_destroy(pp);
+    luxb200_rns_plan_destroy(h->full);
+    luxb200_rns_plan_destroy(h->down);
+    delete h;
+}
+uint32_t luxb200_hks_num_digits(luxb200_hks_plan* h) { return h ? h->nd : 0; }
+
+// c [count][sizeQl][N] EVALUATION, evk_b / evk_a [nd][sizeQ + sizeP][N], out [count][2][sizeQl][N]; t = 0 CKKS, t > 0 BGV.  Host buffers.
+int luxb200_hks_keyswitch(luxb200_hks_plan* h, const uint64_t* c, const uint64_t* evk_b, const uint64_t* evk_a, uint64_t* out,
+                          uint64_t count, uint64_t t) {
+    if (!h || !c || !evk_b || !evk_a || !out) return lb_fail(LUXB200_ERR_INVALID_ARG, "null argument");
+    if (count == 0) return 0;
+    LB_TRY(lb_set_device(h->device));
+    const uint32_t N = h->N, sq = h->sizeQ, sp_ = h->sizeP, sql = h->sizeQl, nd = h->nd, L = sql + sp_, LK = sq + sp_;
+    cudaStream_t st = h->full->stream;
+    const uint64_t key_el = (uint64_t)nd * LK * N;
+    LB_TRY(h->key.ensure(2 * key_el * 8));
+    LB_CUDA(cudaMemcpyAsync(h->key.p, evk_b, key_el * 8, cudaMemcpyHostToDevice, st));
+    LB_CUDA(cudaMemcpyAsync(h->key.as<u64>() + key_el, evk_a, key_el * 8, cudaMemcpyHostToDevice, st));
+    const uint64_t per = ((uint64_t)sql + 2ull * L + (uint64_t)nd * L + 2ull * L + 2ull * sql) * N * 8;   // device bytes per polynomial
+    const uint64_t chunk = std::max<uint64_t>(1, (1ull << 30) / per);
+    for (uint64_t off = 0; off < count; off += chunk) {
+        const uint64_t m = std::min(chunk, count - off);
+        LB_TRY(h->cin.ensure(m * sql * N * 8)); LB_TRY(h->part_in.ensure(m * h->alpha * N * 8)); LB_TRY(h->part_out.ensure(m * L * N * 8));
+        LB_TRY(h->digits.ensure(m * nd * L * N * 8)); LB_TRY(h->tilda.ensure(m * 2 * L * N * 8)); LB_TRY(h->outb.ensure(m * 2 * sql * N * 8));
+        LB_CUDA(cudaMemcpyAsync(h->cin.p, c + off * sql * N, m * sql * N * 8, cudaMemcpyHostToDevice, st));
+        for (uint32_t part = 0; part < nd; ++part) {
+            const uint32_t start = h->alpha * part, sp = (part == nd - 1) ? sql - start : h->alpha, end = start + sp;
+            auto copy = [&](const u64* in, u32 in_stride, u32 in_off, u64* o, u32 out_stride, u32 out_off, u32 limbs) {
+                if (limbs) rns_copy_limbs_kernel<<<nblk(m * limbs * N, 256), 256, 0, st>>>(in, in_stride, in_off, o, out_stride, out_off, limbs, N, m);
+            };
+            copy(h->cin.as<u64>(), sql, start, h->part_in.as<u64>(), sp, 0, sp);
+            LB_CUDA(cudaGetLastError());
+            LB_CUDA(cudaStreamSynchronize(st));
+            LB_TRY(luxb200_approx_mod_up_dev(h->parts[part], h->part_in.p, h->part_out.p, m));   // [own sp | complement L - sp]
+            u64* dg = h->digits.as<u64>();
+            copy(h->part_out.as<u64>(), L, 0, dg, nd * L, part * L + start, sp);             // own limbs in place (:397-399)
+            copy(h->part_out.as<u64>(), L, sp, dg, nd * L, part * L, start);                 // complement before the part (:394-396)
+            copy(h->part_out.as<u64>(), L, sp + start, dg, nd * L, part * L + end, L - end); // and after it, P included (:400-402)
+            LB_CUDA(cudaGetLastError());
+            LB_CUDA(cudaStreamSynchronize(st));
+        }
+        LB_TRY(luxb200_rns_keyswitch_inner_dev(h->full, h->digits.p, h->key.p, h->key.as<u64>() + key_el, h->tilda.p, m, nd, sql));
+        LB_TRY(luxb200_approx_mod_down_bgv_dev(h->down, h->tilda.p, h->outb.p, 2 * m, t));
+        LB_CUDA(cudaMemcpyAsync(out + off * 2 * sql * N, h->outb.p, m * 2 * sql * N * 8, cudaMemcpyDeviceToHost, st));
+        LB_CUDA(cudaStreamSynchronize(st));
     }
     return 0;
 }

@@ -82,6 +82,10 @@ SIGNATURES = {
     "luxb200_approx_mod_up_dev": (INT, [VP, VP, VP, U64]),
     "luxb200_approx_mod_down_dev": (INT, [VP, VP, VP, U64]),
     "luxb200_approx_mod_switch_bgv": (INT, [VP, VP, VP, U64, INT, U64]),
+    "luxb200_hks_plan_create": (INT, [U32, U32, VP, U32, VP, U32, U32, INT, C.POINTER(VP)]),
+    "luxb200_hks_plan_destroy": (None, [VP]),
+    "luxb200_hks_num_digits": (U32, [VP]),
+    "luxb200_hks_keyswitch": (INT, [VP, VP, VP, VP, VP, U64, U64]),
     "luxb200_rns_keyswitch_inner": (INT, [VP, VP, VP, VP, VP, U64, U32, U32]),
     "luxb200_rns_keyswitch_inner_dev": (INT, [VP, VP, VP, VP, VP, U64, U32, U32]),
     "luxb200_approx_mod_down_bgv_dev": (INT, [VP, VP, VP, U64, U64]),

@@ -218,6 +218,17 @@ int luxb200_rns_keyswitch_inner(luxb200_rns_plan* plan, const uint64_t* digits, 
                                 uint64_t* out, uint64_t count, uint32_t nd, uint32_t sizeQl);
 int luxb200_rns_keyswitch_inner_dev(luxb200_rns_plan* plan, const void* digits_dev, const void* evk_b_dev, const void* evk_a_dev,
                                     void* out_dev, uint64_t count, uint32_t nd, uint32_t sizeQl);
+/* Hybrid key switching of one polynomial as one call: KeySwitchHYBRID::EvalKeySwitchPrecomputeCore (keyswitch-hybrid.cpp:328-412:
+ * digits = parts of `alpha` consecutive limbs of Ql = q[0 .. sizeQl), each raised to Ql u P) and EvalFastKeySwitchCore (:414-436:
+ * inner product with the key, ApproxModDown of both results; t > 0 = BGV).  c [count][sizeQl][N] EVALUATION, evk_b / evk_a
+ * [luxb200_hks_num_digits][sizeQ + sizeP][N], out [count][2][sizeQl][N].  Host buffers. */
+typedef struct luxb200_hks_plan luxb200_hks_plan;
+int luxb200_hks_plan_create(uint32_t N, uint32_t sizeQ, const uint64_t* q, uint32_t sizeP, const uint64_t* p, uint32_t alpha,
+                            uint32_t sizeQl, int device, luxb200_hks_plan** out);
+void luxb200_hks_plan_destroy(luxb200_hks_plan* plan);
+uint32_t luxb200_hks_num_digits(luxb200_hks_plan* plan);
+int luxb200_hks_keyswitch(luxb200_hks_plan* plan, const uint64_t* c, const uint64_t* evk_b, const uint64_t* evk_a, uint64_t* out,
+                          uint64_t count, uint64_t t);
 /* Allocation-free variant of luxb200_approx_switch_crt_basis.  It has no counterpart in the reference and was added
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
  * harnesses that forbid it).  Same arguments, same result; the device staging of the basis-switch kernel is a static device

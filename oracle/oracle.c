@@ -987,6 +987,52 @@ int orc_keyswitch_inner(u32 N, u32 sizeQ, const u64* q, u32 sizeP, const u64* p,
         }
     return 0;
 }
+/* Hybrid key switching of one polynomial (KeySwitchHYBRID::EvalKeySwitchPrecomputeCore, keyswitch-hybrid.cpp:328-412, then
+ * EvalFastKeySwitchCore, :414-436).  c [count][sizeQl][N] EVALUATION over Ql = q[0 .. sizeQl); the digits are the parts of
+ * `alpha` consecutive limbs, each raised to Ql u P by an approximate basis switch from its own limbs to all the others (:377-403);
+ * inner product with the key's b / a vectors [numPart][sizeQ + sizeP][N]; both results brought down by P (ptm as in
+ * orc_approx_mod_down_t).  out [count][2][sizeQl][N]. */
+int orc_hybrid_keyswitch(u32 N, u32 sizeQ, const u64* q, u32 sizeP, const u64* p, u32 alpha, u32 sizeQl, const u64* c, const u64* evk_b,
+                         const u64* evk_a, u64* out, u64 count, u64 ptm) {
+    const u32 L = sizeQl + sizeP;
+    u32 nd = (sizeQl + alpha - 1) / alpha, ndmax = (sizeQ + alpha - 1) / alpha;
+    if (nd > ndmax) nd = ndmax;
+    u64* digits = malloc(sizeof(u64) * count * nd * L * N);
+    u64* tilda = malloc(sizeof(u64) * count * 2 * L * N);
+    u64 *src = malloc(sizeof(u64) * (sizeQ + 1)), *dst = malloc(sizeof(u64) * (sizeQ + sizeP + 1));
+    for (u32 part = 0; part < nd; ++part) {
+        const u32 start = alpha * part, sp = (part == nd - 1) ? sizeQl - start : alpha, end = start + sp, sc = L - sp;
+        for (u32 i = 0; i < sp; ++i) src[i] = q[start + i];
+        for (u32 i = 0, k = 0; i < L; ++i)
+            if (i < start || i >= end) dst[k++] = i < sizeQl ? q[i] : p[i - sizeQl];
+        u64* t = malloc(sizeof(u64) * count * sp * N);
+        u64* s = malloc(sizeof(u64) * count * sc * N);
+        for (u64 ct = 0; ct < count; ++ct)
+            for (u32 i = 0; i < sp; ++i) {
+                memcpy(t + (ct * sp + i) * N, c + (ct * sizeQl + start + i) * N, sizeof(u64) * N);
+                orc_ntt(src[i], orc_root_of_unity(2 * (u64)N, src[i]), N, t + (ct * sp + i) * N, 1, 1, 1);
+            }
+        orc_approx_switch_crt_basis(N, sp, src, sc, dst, t, s, count);
+        for (u64 ct = 0; ct < count; ++ct) {
+            u64* dg = digits + (ct * nd + part) * L * N;
+            for (u32 i = 0, k = 0; i < L; ++i) {
+                if (i >= start && i < end) {
+                    memcpy(dg + (u64)i * N, c + (ct * sizeQl + i) * N, sizeof(u64) * N);
+                } else {
+                    u64* sk = s + (ct * sc + k) * N;
+                    orc_ntt(dst[k], orc_root_of_unity(2 * (u64)N, dst[k]), N, sk, 1, 0, 1);
+                    memcpy(dg + (u64)i * N, sk, sizeof(u64) * N);
+                    ++k;
+                }
+            }
+        }
+        free(t); free(s);
+    }
+    orc_keyswitch_inner(N, sizeQ, q, sizeP, p, sizeQl, nd, digits, evk_b, evk_a, tilda, count);
+    orc_approx_mod_down_t(N, sizeQl, q, sizeP, p, tilda, out, 2 * count, ptm);
+    free(digits); free(tilda); free(src); free(dst);
+    return 0;
+}
 int orc_approx_mod_down(u32 N, u32 sizeQ, const u64* q, u32 sizeP, const u64* p, const u64* x, u64* out, u64 count) {
     return orc_approx_mod_down_t(N, sizeQ, q, sizeP, p, x, out, count, 0);
 }

@@ -85,6 +85,8 @@ int orc_approx_mod_down(uint32_t N, uint32_t sizeQ, const uint64_t* q, uint32_t 
                         uint64_t* out, uint64_t count);
 int orc_keyswitch_inner(uint32_t N, uint32_t sizeQ, const uint64_t* q, uint32_t sizeP, const uint64_t* p, uint32_t sizeQl, uint32_t nd,
                         const uint64_t* digits, const uint64_t* evk_b, const uint64_t* evk_a, uint64_t* out, uint64_t count);
+int orc_hybrid_keyswitch(uint32_t N, uint32_t sizeQ, const uint64_t* q, uint32_t sizeP, const uint64_t* p, uint32_t alpha, uint32_t sizeQl,
+                         const uint64_t* c, const uint64_t* evk_b, const uint64_t* evk_a, uint64_t* out, uint64_t count, uint64_t ptm);
 int orc_approx_mod_down_t(uint32_t N, uint32_t sizeQ, const uint64_t* q, uint32_t sizeP, const uint64_t* p, const uint64_t* x,
                           uint64_t* out, uint64_t count, uint64_t ptm);   /* ptm > 0: the BGV branch */
 double orc_time_bingate(OrcCtx*, int gate, const uint64_t* a1, const uint64_t* b1, const uint64_t* a2,

@@ -714,6 +714,104 @@ int ref_keyswitch_inner(uint32_t N, uint32_t sizeQ, const uint64_t* q, uint32_t 
     }
 }
 
+// Hybrid key switching of one polynomial, composed from the reference's own DCRTPoly primitives in the order of
+// KeySwitchHYBRID::EvalKeySwitchPrecomputeCore (keyswitch-hybrid.cpp:328-412) and EvalFastKeySwitchCore (:414-436): Clone /
+// SetFormat(COEFFICIENT) / ApproxSwitchCRTBasis / SetFormat(EVALUATION) per part, the element loops of :394-403 and :457-477,
+// ApproxModDown twice.  (The member functions themselves need a CryptoContext of src/pke, which oracle/_ref does not build;
+// the tables are those of CryptoParametersRNS::PrecomputeCRTTables for each part.)  Layouts as orc_hybrid_keyswitch.
+int ref_hybrid_keyswitch(uint32_t N, uint32_t sizeQ, const uint64_t* q, uint32_t sizeP, const uint64_t* p, uint32_t alpha, uint32_t sizeQl,
+                         const uint64_t* c, const uint64_t* evk_b, const uint64_t* evk_a, uint64_t* out, uint64_t count, uint64_t ptm) {
+    try {
+        auto mk = [&](const std::vector<NativeInteger>& m) {
+            std::vector<NativeInteger> r;
+            for (auto& x : m) r.push_back(RootOfUnity<NativeInteger>(2 * N, x));
+            return std::make_shared<ILDCRTParams<BigInteger>>(2 * N, m, r);
+        };
+        std::vector<NativeInteger> mql, mp, mqlp, mqp;
+        for (uint32_t i = 0; i < sizeQl; ++i) mql.emplace_back(q[i]);
+        for (uint32_t j = 0; j < sizeP; ++j) mp.emplace_back(p[j]);
+        mqlp = mql; mqlp.insert(mqlp.end(), mp.begin(), mp.end());
+        for (uint32_t i = 0; i < sizeQ; ++i) mqp.emplace_back(q[i]);
+        mqp.insert(mqp.end(), mp.begin(), mp.end());
+        auto paramsQl = mk(mql), paramsP = mk(mp), paramsQlP = mk(mqlp), paramsQP = mk(mqp);
+        const uint32_t L = sizeQl + sizeP, LK = sizeQ + sizeP;
+        uint32_t nd = (sizeQl + alpha - 1) / alpha;
+        if (nd > (sizeQ + alpha - 1) / alpha) nd = (sizeQ + alpha - 1) / alpha;
+        auto fill = [&](DCRTPoly& d, const uint64_t* src, uint32_t limbs) {
+            for (uint32_t l = 0; l < limbs; ++l) {
+                NativePoly& limb = d.GetAllElements()[l];
+                for (uint32_t k = 0; k < N; ++k) limb[k] = NativeInteger(src[(size_t)l * N + k]);
+            }
+        };
+        std::vector<DCRTPoly> bv, av;
+        for (uint32_t j = 0; j < nd; ++j) {
+            bv.emplace_back(paramsQP, Format::EVALUATION, true); fill(bv.back(), evk_b + (size_t)j * LK * N, LK);
+            av.emplace_back(paramsQP, Format::EVALUATION, true); fill(av.back(), evk_a + (size_t)j * LK * N, LK);
+        }
+        const RnsTables down = rns_tables(mp, mql);
+        std::vector<NativeInteger> pInv, pInvPrecon, tInvModp, tInvModpPrecon, tModqPrecon;
+        BigInteger Pbig(1);
+        for (auto& m : mp) Pbig *= BigInteger(m.ConvertToInt<uint64_t>());
+        for (auto& qi : mql) {
+            NativeInteger inv = NativeInteger(Pbig.Mod(BigInteger(qi.ConvertToInt<uint64_t>())).ConvertToInt<uint64_t>()).ModInverse(qi);
+            pInv.push_back(inv); pInvPrecon.push_back(inv.PrepModMulConst(qi));
+        }
+        const NativeInteger t(ptm);
+        if (ptm) {
+            for (auto& pj : mp) { tInvModp.push_back(t.ModInverse(pj)); tInvModpPrecon.push_back(tInvModp.back().PrepModMulConst(pj)); }
+            for (auto& qi : mql) tModqPrecon.push_back(t.Mod(qi).PrepModMulConst(qi));
+        }
+        for (uint64_t ct = 0; ct < count; ++ct) {
+            DCRTPoly cpoly(paramsQl, Format::EVALUATION, true);
+            fill(cpoly, c + (size_t)ct * sizeQl * N, sizeQl);
+            std::vector<DCRTPoly> partsCtExt(nd);
+            for (uint32_t part = 0; part < nd; ++part) {
+                const uint32_t start = alpha * part, sp = (part == nd - 1) ? sizeQl - start : alpha, end = start + sp;
+                std::vector<NativeInteger> msrc, mdst;
+                for (uint32_t i = 0; i < sp; ++i) msrc.push_back(mql[start + i]);
+                for (uint32_t i = 0; i < L; ++i)
+                    if (i < start || i >= end) mdst.push_back(mqlp[i]);
+                auto paramsPart = mk(msrc), paramsCompl = mk(mdst);
+                DCRTPoly partCt(paramsPart, Format::EVALUATION, true);
+                for (uint32_t i = 0, idx = start; i < sp; ++i, ++idx) partCt.SetElementAtIndex(i, cpoly.GetElementAtIndex(idx));
+                auto partCtClone = partCt.Clone();
+                partCtClone.SetFormat(Format::COEFFICIENT);
+                const RnsTables T = rns_tables(msrc, mdst);
+                DCRTPoly compl_ = partCtClone.ApproxSwitchCRTBasis(paramsPart, paramsCompl, T.hatInv, T.hatInvPrecon, T.hatMod, T.mu);
+                compl_.SetFormat(Format::EVALUATION);
+                partsCtExt[part] = DCRTPoly(paramsQlP, Format::EVALUATION, true);
+                for (uint32_t i = 0; i < start; ++i) partsCtExt[part].SetElementAtIndex(i, compl_.GetElementAtIndex(i));
+                for (uint32_t i = start, idx = 0; i < end; ++i, ++idx) partsCtExt[part].SetElementAtIndex(i, partCt.GetElementAtIndex(idx));
+                for (uint32_t i = end; i < L; ++i) partsCtExt[part].SetElementAtIndex(i, compl_.GetElementAtIndex(i - sp));
+            }
+            DCRTPoly cTilda0(paramsQlP, Format::EVALUATION, true), cTilda1(paramsQlP, Format::EVALUATION, true);
+            for (uint32_t j = 0; j < nd; ++j) {
+                const DCRTPoly& cj = partsCtExt[j];
+                for (uint32_t i = 0; i < sizeQl; ++i) {
+                    cTilda0.SetElementAtIndex(i, cTilda0.GetElementAtIndex(i) + cj.GetElementAtIndex(i) * bv[j].GetElementAtIndex(i));
+                    cTilda1.SetElementAtIndex(i, cTilda1.GetElementAtIndex(i) + cj.GetElementAtIndex(i) * av[j].GetElementAtIndex(i));
+                }
+                for (uint32_t i = sizeQl, idx = sizeQ; i < L; ++i, ++idx) {
+                    cTilda0.SetElementAtIndex(i, cTilda0.GetElementAtIndex(i) + cj.GetElementAtIndex(i) * bv[j].GetElementAtIndex(idx));
+                    cTilda1.SetElementAtIndex(i, cTilda1.GetElementAtIndex(i) + cj.GetElementAtIndex(i) * av[j].GetElementAtIndex(idx));
+                }
+            }
+            DCRTPoly* both[2] = {&cTilda0, &cTilda1};
+            for (int w = 0; w < 2; ++w) {
+                DCRTPoly r = both[w]->ApproxModDown(paramsQl, paramsP, pInv, pInvPrecon, down.hatInv, down.hatInvPrecon, down.hatMod, down.mu,
+                                                    tInvModp, tInvModpPrecon, t, tModqPrecon);
+                for (uint32_t l = 0; l < sizeQl; ++l)
+                    for (uint32_t k = 0; k < N; ++k)
+                        out[(((size_t)ct * 2 + w) * sizeQl + l) * N + k] = r.GetAllElements()[l][k].ConvertToInt<uint64_t>();
+            }
+        }
+        return 0;
+    }
+    catch (...) {
+        return -1;
+    }
+}
+
 // ---- CPU baseline timers (bench.py --impl reference / cpu_baseline) --------------------------------
 // `count` EvalBinGate(gate) on count ciphertext pairs, outer OMP loop over independent gates — the shape
 // of EvalBinGateBatch (src/binfhe/lib/batch/batch.cpp:197-200). Returns seconds.

@@ -84,6 +84,7 @@ def oracle():
             _sig(fn, INT, [U32, U32, VP, U32, VP, VP, VP, U64])
         _sig(L.orc_approx_mod_down_t, INT, [U32, U32, VP, U32, VP, VP, VP, U64, U64])
         _sig(L.orc_keyswitch_inner, INT, [U32, U32, VP, U32, VP, U32, U32, VP, VP, VP, VP, U64])
+        _sig(L.orc_hybrid_keyswitch, INT, [U32, U32, VP, U32, VP, U32, U32, VP, VP, VP, VP, U64, U64])
         _sig(L.orc_time_bingate, C.c_double, [VP, INT, VP, VP, VP, VP, VP, VP, U64, INT])
         _sig(L.orc_max_threads, INT, [])
         _oracle = L
@@ -136,6 +137,7 @@ def ref():
         _sig(L.ref_rns_op, INT, [U32, U32, VP, U32, VP, VP, VP, U64, INT])
         _sig(L.ref_rns_moddown_t, INT, [U32, U32, VP, U32, VP, VP, VP, U64, U64])
         _sig(L.ref_keyswitch_inner, INT, [U32, U32, VP, U32, VP, U32, U32, VP, VP, VP, VP, U64])
+        _sig(L.ref_hybrid_keyswitch, INT, [U32, U32, VP, U32, VP, U32, U32, VP, VP, VP, VP, U64, U64])
         _sig(L.ref_time_bingate, C.c_double, [VP, INT, VP, VP, VP, VP, VP, VP, U64, INT])
         _sig(L.ref_time_ntt, C.c_double, [U64, U64, U32, VP, U64, INT, INT])
         _sig(L.ref_max_threads, INT, [])

@@ -574,6 +574,35 @@ def test_n2048_pipelined_host_path_matches_small_batches():
     ctx.close()
 
 
+@pytest.mark.parametrize("N,sizeQ,sizeP,alpha,sizeQl,bits,t", [(1024, 4, 2, 2, 4, 50, 0), (4096, 5, 3, 2, 5, 60, 65537), (16384, 6, 2, 3, 4, 55, 0),
+                                                               (2048, 3, 3, 1, 3, 58, 0), (65536, 4, 4, 4, 4, 60, 0)])
+def test_hybrid_keyswitch_vs_oracle(N, sizeQ, sizeP, alpha, sizeQl, bits, t):
+    """luxb200_hks_keyswitch = KeySwitchHYBRID::EvalKeySwitchPrecomputeCore + EvalFastKeySwitchCore (keyswitch-hybrid.cpp:328-436) of one
+    polynomial: digit split, per-digit basis raise, inner product with the key, ApproxModDown of both results — every residue
+    against the oracle (pinned to the reference's DCRTPoly primitives composed in the reference's order, CPU test).  Part sizes
+    that do and do not divide the limb count, a truncated chain, CKKS and BGV, N up to 2^16."""
+    from fhe_b200.context import HybridKeySwitchPlan
+    O = oracle()
+    chain = np.zeros(sizeQ + sizeP, np.uint64); psi = chain.copy()
+    O.orc_dcrt_chain(N, sizeQ + sizeP, bits, P(chain), P(psi))
+    q, p = np.ascontiguousarray(chain[:sizeQ]), np.ascontiguousarray(chain[sizeQ:])
+    rng = np.random.default_rng(N + alpha)
+    cnt = 2
+    pl = HybridKeySwitchPlan(N, q, p, alpha, sizeQl)
+    nd = pl.num_digits
+    assert nd == min(-(-sizeQl // alpha), -(-sizeQ // alpha))
+    c = np.stack([np.stack([rng.integers(0, int(m), size=N, dtype=np.uint64) for m in q[:sizeQl]]) for _ in range(cnt)])
+    c[0, 0, :] = q[0] - np.uint64(1)
+    kb = np.stack([np.stack([rng.integers(0, int(m), size=N, dtype=np.uint64) for m in chain]) for _ in range(nd)])
+    ka = np.stack([np.stack([rng.integers(0, int(m), size=N, dtype=np.uint64) for m in chain]) for _ in range(nd)])
+    ref = np.zeros((cnt, 2, sizeQl, N), np.uint64)
+    assert O.orc_hybrid_keyswitch(N, sizeQ, P(q), sizeP, P(p), alpha, sizeQl, P(c), P(kb), P(ka), P(ref), cnt, t) == 0
+    got = pl.KeySwitch(c, kb, ka, t)
+    assert (got == ref).all()
+    assert (pl.KeySwitch(c, kb, ka, t) == got).all()   # a second call on the same plan (cached tables, reused buffers)
+    pl.close()
+
+
 # ---- key-ordered key switch (ks_tile.cuh): the 16-bit keys of the qKS = 2^14, baseKS = 32 sets ---------------------------------
 @pytest.mark.parametrize("n,N,method,cnt", [(503, 1024, "GINX", 700), (447, 1024, "LMKCDEY", 257), (40, 512, "GINX", 1000)])
 def test_keyswitch_tile_vs_oracle_and_gather_kernel(n, N, method, cnt, monkeypatch):

@@ -207,6 +207,17 @@ def test_rns_basis_conversion_pins_the_oracle(N, sizeQ, sizeP, bits):
     assert R.ref_keyswitch_inner(N, sizeQ, P(q), sizeP, P(p), sizeQl, nd, P(dg), P(kb), P(ka), P(a), cnt) == 0
     assert O.orc_keyswitch_inner(N, sizeQ, P(q), sizeP, P(p), sizeQl, nd, P(dg), P(kb), P(ka), P(b), cnt) == 0
     assert (a == b).all()
+    # the whole hybrid key switch of one polynomial (EvalKeySwitchPrecomputeCore + EvalFastKeySwitchCore), CKKS and BGV, on the full
+    # chain and on a truncated one, with part sizes that do and do not divide the limb count
+    for alpha, sizeQl2, t in ((1, sizeQ, 0), (2, sizeQ, 65537), (2, max(1, sizeQ - 1), 0), (sizeQ, sizeQ, 0)):
+        nd2 = min((sizeQl2 + alpha - 1) // alpha, (sizeQ + alpha - 1) // alpha)
+        cin = np.stack([np.stack([rng.integers(0, int(m), size=N, dtype=np.uint64) for m in q[:sizeQl2]]) for _ in range(cnt)])
+        kb2 = np.stack([np.stack([rng.integers(0, int(m), size=N, dtype=np.uint64) for m in chain]) for _ in range(nd2)])
+        ka2 = np.stack([np.stack([rng.integers(0, int(m), size=N, dtype=np.uint64) for m in chain]) for _ in range(nd2)])
+        a = np.zeros((cnt, 2, sizeQl2, N), np.uint64); b = a.copy()
+        assert R.ref_hybrid_keyswitch(N, sizeQ, P(q), sizeP, P(p), alpha, sizeQl2, P(cin), P(kb2), P(ka2), P(a), cnt, t) == 0
+        assert O.orc_hybrid_keyswitch(N, sizeQ, P(q), sizeP, P(p), alpha, sizeQl2, P(cin), P(kb2), P(ka2), P(b), cnt, t) == 0
+        assert (a == b).all(), (alpha, sizeQl2, t)
     # the BGV branch of ApproxModDown (plaintext modulus t > 0; tables of bgvrns-cryptoparameters.cpp:78-95)
     for t in (65537, 2, (1 << 40) + 15):
         a = np.zeros((cnt, sizeQ, N), np.uint64); b = a.copy()
