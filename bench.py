@@ -424,6 +424,55 @@ def n2048_metric(lib, local, name, G, imad_peak):
     return out
 
 
+def hks_metric(lib, local, dev, peaks, imad_peak, count=32, iters=5):
+    """SURVEY 8(f) rank 4 at the BASELINE configs[4] ring: hybrid key switching (KeySwitchHYBRID::KeySwitchCore,
+    keyswitch-hybrid.cpp:328-436) of `count` polynomials at N = 2^16 over 24 + 8 sixty-bit limbs, 3 digits of 8 limbs, key and data
+    resident in HBM (luxb200_hks_keyswitch_dev).  Parity of the timed call: polynomial 0 against the oracle.  Work per key
+    switch: 3 x (8 INTT + 24 NTT) + 2 x (8 INTT + 24 NTT) = 160 limb transforms; algorithmic traffic = c in, digits out and in,
+    key in, both accumulators out and in, result out."""
+    import torch
+    from fhe_b200.context import HybridKeySwitchPlan
+    sys.path.insert(0, os.path.join(ROOT, "tests"))
+    from orclib import P, oracle
+    O = oracle()
+    N, sizeQ, sizeP, alpha = 65536, 24, 8, 8
+    chain = np.zeros(sizeQ + sizeP, np.uint64); psi = chain.copy()
+    O.orc_dcrt_chain(N, sizeQ + sizeP, 60, P(chain), P(psi))
+    q, p = np.ascontiguousarray(chain[:sizeQ]), np.ascontiguousarray(chain[sizeQ:])
+    pl = HybridKeySwitchPlan(N, q, p, alpha, sizeQ, device=local)
+    nd, L = pl.num_digits, sizeQ + sizeP
+    rng = np.random.default_rng(16)
+    c = np.stack([np.stack([rng.integers(0, int(m), size=N, dtype=np.uint64) for m in q]) for _ in range(count)])
+    kb = np.stack([np.stack([rng.integers(0, int(m), size=N, dtype=np.uint64) for m in chain]) for _ in range(nd)])
+    ka = np.stack([np.stack([rng.integers(0, int(m), size=N, dtype=np.uint64) for m in chain]) for _ in range(nd)])
+    d_c = torch.from_numpy(c.view(np.int64)).to(dev); d_kb = torch.from_numpy(kb.view(np.int64)).to(dev)
+    d_ka = torch.from_numpy(ka.view(np.int64)).to(dev)
+    d_out = torch.empty((count, 2, sizeQ, N), dtype=torch.int64, device=dev)
+    torch.cuda.synchronize()
+    run = lambda: pl.KeySwitchDev(d_c.data_ptr(), d_kb.data_ptr(), d_ka.data_ptr(), d_out.data_ptr(), count, 0)
+    run(); run()
+    times = []
+    for _ in range(iters):
+        t0 = time.perf_counter(); run(); times.append(time.perf_counter() - t0)
+    ms = 1e3 * min(times) / count
+    ref = np.zeros((1, 2, sizeQ, N), np.uint64)
+    O.orc_hybrid_keyswitch(N, sizeQ, P(q), sizeP, P(p), alpha, sizeQ, P(np.ascontiguousarray(c[:1])), P(kb), P(ka), P(ref), 1, 0)
+    parity = bool((d_out[:1].cpu().numpy().view(np.uint64) == ref).all())
+    transforms = nd * L + 2 * L
+    bfly = transforms * (N // 2) * 16
+    limbs_moved = sizeQ + 2 * nd * L + 2 * nd * L + 2 * 2 * L + 2 * sizeQ   # c, digits w + r, key b + a, accumulators w + r, result
+    gbs = limbs_moved * N * 8 / (ms * 1e-3) / 1e9
+    pl.close()
+    return {"workload": f"hybrid key switch, N={N}, {sizeQ}+{sizeP} limbs of 60 bits, {nd} digits x {alpha} limbs, {count} polynomials resident in HBM",
+            "ms_per_keyswitch": ms, "keyswitches_per_s": 1e3 / ms, "parity": parity,
+            "Gbutterfly_s": bfly / (ms * 1e-3) / 1e9, "limb_transforms": transforms,
+            "roofline": {"bound": "int-pipe (the NTTs)", "peak_Gbutterfly_s": imad_peak / 14 / 1e9 if imad_peak else None,
+                         "frac": (bfly / (ms * 1e-3)) / (imad_peak / 14) if imad_peak else None,
+                         "algorithmic_GBs": gbs, "hbm_peak_gbs": peaks.get("hbm_gbs"),
+                         "frac_hbm": gbs / peaks["hbm_gbs"] if peaks.get("hbm_gbs") else None,
+                         "note": "functional composite: existing kernels with a stream synchronisation between steps (DESIGN 4.8, 8)"}}
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
@@ -645,6 +694,7 @@ def main():
         extras["ntt32_n2048"] = ntt32_metric(lib, local, dev, 2048, 29)
         extras["lmkcdey"] = method_metric(lib, local, dev, "STD128_LMKCDEY", "LMKCDEY", 16384, imad_v)
         extras["ap"] = method_metric(lib, local, dev, "STD128_AP", "AP", 4096, imad_v)
+        extras["hks_n65536"] = hks_metric(lib, local, dev, _peaks(), imad_v)
         # 1776 gates = whole waves for 3 (two digits), 2 (three digits) and 3 (shared-memory kernel) ciphertexts per SM
         extras["n2048"] = {k: n2048_metric(lib, local, k, 1776, imad_v) for k in ("STD256", "STD256_3", "STD192")}
 

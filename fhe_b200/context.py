@@ -487,6 +487,10 @@ class HybridKeySwitchPlan:
         _l.check(self.L.luxb200_hks_keyswitch(self.h, _l.ptr(c), _l.ptr(evk_b), _l.ptr(evk_a), _l.ptr(out), c.shape[0], int(t)))
         return out
 
+    def KeySwitchDev(self, c_ptr, evk_b_ptr, evk_a_ptr, out_ptr, count, t=0):
+        """device pointers (ints) on the plan's device; returns when the result is complete"""
+        _l.check(self.L.luxb200_hks_keyswitch_dev(self.h, _l.ptr(c_ptr), _l.ptr(evk_b_ptr), _l.ptr(evk_a_ptr), _l.ptr(out_ptr), int(count), int(t)))
+
     def close(self):
         if self.h:
             self.L.luxb200_hks_plan_destroy(self.h)

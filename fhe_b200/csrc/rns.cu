@@ -515,31 +515,19 @@ void luxb200_hks_plan_destroy(luxb200_hks_plan* h) {
 }
 uint32_t luxb200_hks_num_digits(luxb200_hks_plan* h) { return h ? h->nd : 0; }
 
-// c [count][sizeQl][N] EVALUATION, evk_b / evk_a [nd][sizeQ + sizeP][N], out [count][2][sizeQl][N]; t = 0 CKKS, t > 0 BGV.  Host buffers.
-int luxb200_hks_keyswitch(luxb200_hks_plan* h, const uint64_t* c, const uint64_t* evk_b, const uint64_t* evk_a, uint64_t* out,
-                          uint64_t count, uint64_t t) {
-    if (!h || !c || !evk_b || !evk_a || !out) return lb_fail(LUXB200_ERR_INVALID_ARG, "null argument");
-    if (count == 0) return 0;
-    LB_TRY(lb_set_device(h->device));
-    const uint32_t N = h->N, sq = h->sizeQ, sp_ = h->sizeP, sql = h->sizeQl, nd = h->nd, L = sql + sp_, LK = sq + sp_;
+// the device part for m polynomials: c_dev [m][sizeQl][N], keys [nd][sizeQ + sizeP][N], out_dev [m][2][sizeQl][N]
+static int hks_run(luxb200_hks_plan* h, const u64* c_dev, const u64* kb_dev, const u64* ka_dev, u64* out_dev, uint64_t m, uint64_t t) {
+    const uint32_t N = h->N, sp_ = h->sizeP, sql = h->sizeQl, nd = h->nd, L = sql + sp_;
     cudaStream_t st = h->full->stream;
-    const uint64_t key_el = (uint64_t)nd * LK * N;
-    LB_TRY(h->key.ensure(2 * key_el * 8));
-    LB_CUDA(cudaMemcpyAsync(h->key.p, evk_b, key_el * 8, cudaMemcpyHostToDevice, st));
-    LB_CUDA(cudaMemcpyAsync(h->key.as<u64>() + key_el, evk_a, key_el * 8, cudaMemcpyHostToDevice, st));
-    const uint64_t per = ((uint64_t)sql + 2ull * L + (uint64_t)nd * L + 2ull * L + 2ull * sql) * N * 8;   // device bytes per polynomial
-    const uint64_t chunk = std::max<uint64_t>(1, (1ull << 30) / per);
-    for (uint64_t off = 0; off < count; off += chunk) {
-        const uint64_t m = std::min(chunk, count - off);
-        LB_TRY(h->cin.ensure(m * sql * N * 8)); LB_TRY(h->part_in.ensure(m * h->alpha * N * 8)); LB_TRY(h->part_out.ensure(m * L * N * 8));
-        LB_TRY(h->digits.ensure(m * nd * L * N * 8)); LB_TRY(h->tilda.ensure(m * 2 * L * N * 8)); LB_TRY(h->outb.ensure(m * 2 * sql * N * 8));
-        LB_CUDA(cudaMemcpyAsync(h->cin.p, c + off * sql * N, m * sql * N * 8, cudaMemcpyHostToDevice, st));
+    {
+        LB_TRY(h->part_in.ensure(m * h->alpha * N * 8)); LB_TRY(h->part_out.ensure(m * L * N * 8));
+        LB_TRY(h->digits.ensure(m * nd * L * N * 8)); LB_TRY(h->tilda.ensure(m * 2 * L * N * 8));
         for (uint32_t part = 0; part < nd; ++part) {
             const uint32_t start = h->alpha * part, sp = (part == nd - 1) ? sql - start : h->alpha, end = start + sp;
             auto copy = [&](const u64* in, u32 in_stride, u32 in_off, u64* o, u32 out_stride, u32 out_off, u32 limbs) {
                 if (limbs) rns_copy_limbs_kernel<<<nblk(m * limbs * N, 256), 256, 0, st>>>(in, in_stride, in_off, o, out_stride, out_off, limbs, N, m);
             };
-            copy(h->cin.as<u64>(), sql, start, h->part_in.as<u64>(), sp, 0, sp);
+            copy(c_dev, sql, start, h->part_in.as<u64>(), sp, 0, sp);
             LB_CUDA(cudaGetLastError());
             LB_CUDA(cudaStreamSynchronize(st));
             LB_TRY(luxb200_approx_mod_up_dev(h->parts[part], h->part_in.p, h->part_out.p, m));   // [own sp | complement L - sp]
@@ -550,8 +538,50 @@ int luxb200_hks_keyswitch(luxb200_hks_plan* h, const uint64_t* c, const uint64_t
             LB_CUDA(cudaGetLastError());
             LB_CUDA(cudaStreamSynchronize(st));
         }
-        LB_TRY(luxb200_rns_keyswitch_inner_dev(h->full, h->digits.p, h->key.p, h->key.as<u64>() + key_el, h->tilda.p, m, nd, sql));
-        LB_TRY(luxb200_approx_mod_down_bgv_dev(h->down, h->tilda.p, h->outb.p, 2 * m, t));
+        LB_TRY(luxb200_rns_keyswitch_inner_dev(h->full, h->digits.p, kb_dev, ka_dev, h->tilda.p, m, nd, sql));
+        LB_TRY(luxb200_approx_mod_down_bgv_dev(h->down, h->tilda.p, out_dev, 2 * m, t));
+    }
+    return 0;
+}
+static uint64_t hks_chunk(const luxb200_hks_plan* h) {
+    const uint64_t L = h->sizeQl + h->sizeP;
+    const uint64_t per = ((uint64_t)h->sizeQl + 2 * L + (uint64_t)h->nd * L + 2 * L + 2ull * h->sizeQl) * h->N * 8;   // device bytes per polynomial
+    return std::max<uint64_t>(1, (8ull << 30) / per);   // up to 8 GB of work buffers: 56 polynomials at N = 2^16 with 24 + 8 limbs
+}
+// c [count][sizeQl][N] EVALUATION, evk_b / evk_a [nd][sizeQ + sizeP][N], out [count][2][sizeQl][N]; t = 0 CKKS, t > 0 BGV.  Device
+// pointers on the plan's device (the key stays resident between calls); returns when the result is complete.
+int luxb200_hks_keyswitch_dev(luxb200_hks_plan* h, const void* c_dev, const void* evk_b_dev, const void* evk_a_dev, void* out_dev,
+                              uint64_t count, uint64_t t) {
+    if (!h || !c_dev || !evk_b_dev || !evk_a_dev || !out_dev) return lb_fail(LUXB200_ERR_INVALID_ARG, "null argument");
+    if (count == 0) return 0;
+    LB_TRY(lb_set_device(h->device));
+    const uint64_t chunk = hks_chunk(h), in_el = (uint64_t)h->sizeQl * h->N;
+    for (uint64_t off = 0; off < count; off += chunk) {
+        const uint64_t m = std::min(chunk, count - off);
+        LB_TRY(hks_run(h, reinterpret_cast<const u64*>(c_dev) + off * in_el, reinterpret_cast<const u64*>(evk_b_dev),
+                       reinterpret_cast<const u64*>(evk_a_dev), reinterpret_cast<u64*>(out_dev) + off * 2 * in_el, m, t));
+    }
+    return 0;
+}
+// the same with host buffers
+int luxb200_hks_keyswitch(luxb200_hks_plan* h, const uint64_t* c, const uint64_t* evk_b, const uint64_t* evk_a, uint64_t* out,
+                          uint64_t count, uint64_t t) {
+    if (!h || !c || !evk_b || !evk_a || !out) return lb_fail(LUXB200_ERR_INVALID_ARG, "null argument");
+    if (count == 0) return 0;
+    LB_TRY(lb_set_device(h->device));
+    const uint32_t N = h->N, sql = h->sizeQl;
+    cudaStream_t st = h->full->stream;
+    const uint64_t key_el = (uint64_t)h->nd * (h->sizeQ + h->sizeP) * N;
+    LB_TRY(h->key.ensure(2 * key_el * 8));
+    LB_CUDA(cudaMemcpyAsync(h->key.p, evk_b, key_el * 8, cudaMemcpyHostToDevice, st));
+    LB_CUDA(cudaMemcpyAsync(h->key.as<u64>() + key_el, evk_a, key_el * 8, cudaMemcpyHostToDevice, st));
+    const uint64_t chunk = hks_chunk(h);
+    for (uint64_t off = 0; off < count; off += chunk) {
+        const uint64_t m = std::min(chunk, count - off);
+        LB_TRY(h->cin.ensure(m * sql * N * 8)); LB_TRY(h->outb.ensure(m * 2 * sql * N * 8));
+        LB_CUDA(cudaMemcpyAsync(h->cin.p, c + off * sql * N, m * sql * N * 8, cudaMemcpyHostToDevice, st));
+        LB_CUDA(cudaStreamSynchronize(st));
+        LB_TRY(hks_run(h, h->cin.as<u64>(), h->key.as<u64>(), h->key.as<u64>() + key_el, h->outb.as<u64>(), m, t));
         LB_CUDA(cudaMemcpyAsync(out + off * 2 * sql * N, h->outb.p, m * 2 * sql * N * 8, cudaMemcpyDeviceToHost, st));
         LB_CUDA(cudaStreamSynchronize(st));
     }

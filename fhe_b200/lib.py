@@ -86,6 +86,7 @@ SIGNATURES = {
     "luxb200_hks_plan_destroy": (None, [VP]),
     "luxb200_hks_num_digits": (U32, [VP]),
     "luxb200_hks_keyswitch": (INT, [VP, VP, VP, VP, VP, U64, U64]),
+    "luxb200_hks_keyswitch_dev": (INT, [VP, VP, VP, VP, VP, U64, U64]),
     "luxb200_rns_keyswitch_inner": (INT, [VP, VP, VP, VP, VP, U64, U32, U32]),
     "luxb200_rns_keyswitch_inner_dev": (INT, [VP, VP, VP, VP, VP, U64, U32, U32]),
     "luxb200_approx_mod_down_bgv_dev": (INT, [VP, VP, VP, U64, U64]),

@@ -229,6 +229,9 @@ void luxb200_hks_plan_destroy(luxb200_hks_plan* plan);
 uint32_t luxb200_hks_num_digits(luxb200_hks_plan* plan);
 int luxb200_hks_keyswitch(luxb200_hks_plan* plan, const uint64_t* c, const uint64_t* evk_b, const uint64_t* evk_a, uint64_t* out,
                           uint64_t count, uint64_t t);
+/* the same on device pointers (plan's device; the key stays resident between calls); returns when the result is complete */
+int luxb200_hks_keyswitch_dev(luxb200_hks_plan* plan, const void* c_dev, const void* evk_b_dev, const void* evk_a_dev, void* out_dev,
+                              uint64_t count, uint64_t t);
 /* Allocation-free variant of luxb200_approx_switch_crt_basis.  It has no counterpart in the reference and was added
  * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops,
  * harnesses that forbid it).  Same arguments, same result; the device staging of the basis-switch kernel is a static device
